@@ -1,0 +1,196 @@
+// api_io.inl -- host <-> HBM transfers, sparse mutators, frame dumps, statistics.
+// Included at the end of fluid_cuda.cu.
+
+static int check_field(fluid_handle* h, int id, const char* who)
+{
+    if (!h) return FLUID_E_ARG;
+    if (id < 0 || id >= FLUID_NFIELDS) return fl_fail(h, FLUID_E_ARG, "%s: bad field id %d", who, id);
+    return 0;
+}
+
+// offset (floats) of this slab's first local plane (zl = 0) inside the GLOBAL reference volume
+static size_t slab_host_offset(const fluid_handle* h) { return ref_plane_floats(h->g) * (size_t)(h->g.zlo - 1); }
+static size_t slab_host_floats(const fluid_handle* h) { return ref_plane_floats(h->g) * (size_t)(h->g.Dl + 2); }
+
+extern "C" {
+
+int fluid_upload_field(fluid_handle* h, int field_id, const float* padded_host)
+{
+    if (int e = check_field(h, field_id, "fluid_upload_field")) return e;
+    if (!padded_host) return fl_fail(h, FLUID_E_ARG, "fluid_upload_field: null host pointer");
+    FL_CUDA(h, cudaMemcpyAsync(h->staging, padded_host + slab_host_offset(h),
+                               slab_host_floats(h) * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    k_unpack<<<fl_grid_1d((long long)slab_host_floats(h)), 256, 0, h->stream>>>(h->g, h->staging,
+                                                                                 h->field[field_id]);
+    FL_CHECK_LAUNCH(h);
+    if (field_id == FLUID_OBS) h->flags_dirty = true;
+    // the staging buffer is reused by the next transfer: keep host-visible ordering simple
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int fluid_download_field(fluid_handle* h, int field_id, float* padded_host)
+{
+    if (int e = check_field(h, field_id, "fluid_download_field")) return e;
+    if (!padded_host) return fl_fail(h, FLUID_E_ARG, "fluid_download_field: null host pointer");
+    k_pack<<<fl_grid_1d((long long)slab_host_floats(h)), 256, 0, h->stream>>>(h->g, h->field[field_id],
+                                                                               h->staging);
+    FL_CHECK_LAUNCH(h);
+    // a slab returns its OWNED planes only: interior planes plus the global ghost plane(s) it holds
+    const size_t pf = ref_plane_floats(h->g);
+    const int first = (h->rank == 0) ? 0 : 1;
+    const int last = (h->rank == h->nranks - 1) ? h->g.Dl + 1 : h->g.Dl;
+    FL_CUDA(h, cudaMemcpyAsync(padded_host + slab_host_offset(h) + pf * first, h->staging + pf * first,
+                               pf * (size_t)(last - first + 1) * sizeof(float), cudaMemcpyDeviceToHost,
+                               h->stream));
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int fluid_upload_obstacles(fluid_handle* h, const float* obs_padded)
+{
+    if (int e = fluid_upload_field(h, FLUID_OBS, obs_padded)) return e;
+    return fl_rebuild_flags(h);
+}
+
+static int sparse_stage(fluid_handle* h, int n, const int* xyz, const float* val, int nval)
+{
+    if (n > h->sparse_cap) {
+        cudaFree(h->d_xyz); cudaFree(h->d_val); h->d_xyz = nullptr; h->d_val = nullptr;
+        int cap = n < 4096 ? 4096 : n;
+        FL_CUDA(h, cudaMalloc(&h->d_xyz, (size_t)cap * 3 * sizeof(int)));
+        FL_CUDA(h, cudaMalloc(&h->d_val, (size_t)cap * 3 * sizeof(float)));
+        h->sparse_cap = cap;
+    }
+    FL_CUDA(h, cudaMemcpyAsync(h->d_xyz, xyz, (size_t)n * 3 * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    if (val) FL_CUDA(h, cudaMemcpyAsync(h->d_val, val, (size_t)n * nval * sizeof(float),
+                                        cudaMemcpyHostToDevice, h->stream));
+    return 0;
+}
+
+static int check_xyz(fluid_handle* h, int n, const int* xyz, const char* who)
+{
+    if (!h) return FLUID_E_ARG;
+    if (n < 0 || (n > 0 && !xyz)) return fl_fail(h, FLUID_E_ARG, "%s: bad arguments", who);
+    for (int i = 0; i < n; ++i)
+        if (xyz[3 * i] < 0 || xyz[3 * i] > h->g.W + 1 || xyz[3 * i + 1] < 0 || xyz[3 * i + 1] > h->g.H + 1 ||
+            xyz[3 * i + 2] < 0 || xyz[3 * i + 2] > h->g.D + 1)
+            return fl_fail(h, FLUID_E_ARG, "%s: cell %d (%d,%d,%d) outside the padded grid", who, i,
+                           xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+    return 0;
+}
+
+int fluid_add_obstacles(fluid_handle* h, int n, const int* xyz)
+{
+    if (int e = check_xyz(h, n, xyz, "fluid_add_obstacles")) return e;
+    if (n == 0) return 0;
+    if (int e = sparse_stage(h, n, xyz, nullptr, 0)) return e;
+    k_add_obstacles<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_OBS], n, h->d_xyz);
+    FL_CHECK_LAUNCH(h);
+    h->flags_dirty = true;
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int fluid_add_density(fluid_handle* h, int n, const int* xyz, const float* amount)
+{
+    if (int e = check_xyz(h, n, xyz, "fluid_add_density")) return e;
+    if (n == 0) return 0;
+    if (!amount) return fl_fail(h, FLUID_E_ARG, "fluid_add_density: null amounts");
+    if (int e = sparse_stage(h, n, xyz, amount, 1)) return e;
+    k_add_density<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_DENS], n, h->d_xyz, h->d_val);
+    FL_CHECK_LAUNCH(h);
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int fluid_set_velocity(fluid_handle* h, int n, const int* xyz, const float* v)
+{
+    if (int e = check_xyz(h, n, xyz, "fluid_set_velocity")) return e;
+    if (n == 0) return 0;
+    if (!v) return fl_fail(h, FLUID_E_ARG, "fluid_set_velocity: null values");
+    if (int e = sparse_stage(h, n, xyz, v, 3)) return e;
+    k_set_velocity<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY],
+                                                          h->field[FLUID_VZ], n, h->d_xyz, h->d_val);
+    FL_CHECK_LAUNCH(h);
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+// frame write of step(), simulation.cpp:140-148: dens, obs, v_x, v_y, v_z.  The fields are
+// repacked to the reference layout on the compute stream (cheap, HBM to HBM), then the D2H copies
+// run on the dump stream so the next time step overlaps the PCIe transfer.
+int fluid_dump_frame_async(fluid_handle* h, float* const dst[5])
+{
+    if (!h || !dst) return FLUID_E_ARG;
+    static const int ids[5] = { FLUID_DENS, FLUID_OBS, FLUID_VX, FLUID_VY, FLUID_VZ };
+    const size_t nfl = slab_host_floats(h);
+    for (int i = 0; i < 5; ++i)
+        if (dst[i] && !h->frame_staging[i]) FL_CUDA(h, cudaMalloc(&h->frame_staging[i], nfl * sizeof(float)));
+    // the previous dump must have left the staging buffers before they are overwritten
+    if (h->frame_in_flight) FL_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_frame_done, 0));
+    for (int i = 0; i < 5; ++i) {
+        if (!dst[i]) continue;
+        k_pack<<<fl_grid_1d((long long)nfl), 256, 0, h->stream>>>(h->g, h->field[ids[i]], h->frame_staging[i]);
+        FL_CHECK_LAUNCH(h);
+    }
+    FL_CUDA(h, cudaEventRecord(h->ev_frame_packed, h->stream));
+    FL_CUDA(h, cudaStreamWaitEvent(h->dump_stream, h->ev_frame_packed, 0));
+    const size_t pf = ref_plane_floats(h->g);
+    const int first = (h->rank == 0) ? 0 : 1;
+    const int last = (h->rank == h->nranks - 1) ? h->g.Dl + 1 : h->g.Dl;
+    for (int i = 0; i < 5; ++i) {
+        if (!dst[i]) continue;
+        FL_CUDA(h, cudaMemcpyAsync(dst[i] + slab_host_offset(h) + pf * first, h->frame_staging[i] + pf * first,
+                                   pf * (size_t)(last - first + 1) * sizeof(float), cudaMemcpyDeviceToHost,
+                                   h->dump_stream));
+    }
+    FL_CUDA(h, cudaEventRecord(h->ev_frame_done, h->dump_stream));
+    h->frame_in_flight = true;
+    return 0;
+}
+
+int fluid_frame_wait(fluid_handle* h)
+{
+    if (!h) return FLUID_E_ARG;
+    if (h->frame_in_flight) { FL_CUDA(h, cudaEventSynchronize(h->ev_frame_done)); h->frame_in_flight = false; }
+    return 0;
+}
+
+// statistics of run() (simulation.cpp:73-90) over the padded cells this slab owns
+int fluid_stats(fluid_handle* h, double out[9])
+{
+    if (!h || !out) return FLUID_E_ARG;
+    const int first = (h->rank == 0) ? 0 : 1;
+    const int last = (h->rank == h->nranks - 1) ? h->g.Dl + 1 : h->g.Dl;
+    const long long n = (long long)(h->g.W + 2) * h->g.rows * (last - first + 1);
+    const int nb = fl_grid_1d(n, 256, h->n_partial);
+    k_stats_partial<<<nb, 256, 0, h->stream>>>(h->g, first, last, h->field[FLUID_DENS], h->field[FLUID_VX],
+                                               h->field[FLUID_VY], h->field[FLUID_VZ], h->d_partial);
+    FL_CHECK_LAUNCH(h);
+    k_stats_final<<<1, 256, 0, h->stream>>>(nb, h->d_partial, h->d_out);
+    FL_CHECK_LAUNCH(h);
+    FL_CUDA(h, cudaMemcpyAsync(out, h->d_out, FL_NSTAT * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int fluid_divergence_norm(fluid_handle* h, double out[2])
+{
+    if (!h || !out) return FLUID_E_ARG;
+    if (int e = fl_rebuild_flags(h)) return e;
+    const long long n = (long long)h->g.W * h->g.H * h->g.Dl;
+    const int nb = fl_grid_1d(n, 256, h->n_partial);
+    k_divnorm_partial<<<nb, 256, 0, h->stream>>>(h->g, h->field[FLUID_DIVERGENCE], h->cflags, h->d_partial);
+    FL_CHECK_LAUNCH(h);
+    std::vector<double> part(2 * (size_t)nb);
+    FL_CUDA(h, cudaMemcpyAsync(part.data(), h->d_partial, part.size() * sizeof(double),
+                               cudaMemcpyDeviceToHost, h->stream));
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    double s = 0.0, m = 0.0;
+    for (int i = 0; i < nb; ++i) { s += part[2 * i]; if (part[2 * i + 1] > m) m = part[2 * i + 1]; }
+    out[0] = sqrt(s); out[1] = m;      // slab mode: caller combines (sum of squares is out[0]^2)
+    return 0;
+}
+
+}  // extern "C"

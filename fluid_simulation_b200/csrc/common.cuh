@@ -1,0 +1,124 @@
+// common.cuh -- grid geometry, HBM layout and small device helpers shared by all kernels.
+//
+// HBM layout (DESIGN.md "Data layout"): every field is a pitched SoA float volume
+//   index(x, y, zl) = XOFF + x + y*pitch + zl*plane,   x in 0..W+1, y in 0..H+1, zl in 0..Dl+1
+// with XOFF = 3 so that the first interior cell x=1 sits on a 16-byte boundary (column 4) and
+// pitch = round_up(W + 2 + XOFF, 4): interior x-rows are float4-aligned and every row stride is a
+// multiple of 16 B (the TMA requirement).  The reference layout (x + y*(W+2) + z*(W+2)*(H+2),
+// simulation.h:9) only exists in the pack/unpack kernels at the host boundary.
+// zl is the LOCAL plane index of a z-slab: global z = zlo + zl - 1 (zlo = 1, Dl = D on one GPU).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define FL_XOFF 3
+
+// per-cell flag byte, built once from obs (k_build_flags)
+#define FL_SOLID   0x01u   // obs == 1.0f                       (simulation.cpp:222, 301, 326, 375)
+#define FL_NOSLIP  0x02u   // fluid cell with an in-domain solid 6-neighbour (simulation.cpp:232-238)
+#define FL_OPEN_XP 0x04u   // i+1 <= W  && obs(i+1) == 0.0f     (simulation.cpp:307, 329)
+#define FL_OPEN_XM 0x08u   // i-1 >= 1  && obs(i-1) == 0.0f
+#define FL_OPEN_YP 0x10u
+#define FL_OPEN_YM 0x20u
+#define FL_OPEN_ZP 0x40u
+#define FL_OPEN_ZM 0x80u
+
+struct Grid {
+    int W, H, D;          // global interior size
+    int Dl, zlo;          // local slab: interior planes and global z of local plane 1
+    int pitch;            // floats per x-row
+    int rows;             // H + 2
+    long long plane;      // pitch * rows
+    long long cells;      // plane * (Dl + 2)   (allocated floats per field)
+    int nxq;              // ceil(W / 4) x-quads per row
+};
+
+__host__ __device__ __forceinline__ long long fl_idx(const Grid& g, int x, int y, int zl)
+{
+    return (long long)FL_XOFF + x + (long long)y * g.pitch + (long long)zl * g.plane;
+}
+
+// velocity component b in {1,2,3} masks solids and no-slip cells, scalars (b == 0) only solids
+__device__ __forceinline__ unsigned fl_zero_mask(int b) { return b == 0 ? FL_SOLID : (FL_SOLID | FL_NOSLIP); }
+
+// thread -> (x-quad, y, zl) mapping used by all "one thread = 4 consecutive x cells" kernels:
+// blockDim = (bx, by), gridDim = (ceil(nxq/bx), ceil(H/by), Dl [* batch])
+struct QuadPos { int x0, y, zl; bool valid; };
+
+__device__ __forceinline__ QuadPos fl_quad_pos(const Grid& g, int zl)
+{
+    QuadPos p;
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    p.x0 = 1 + 4 * q;
+    p.y  = 1 + blockIdx.y * blockDim.y + threadIdx.y;
+    p.zl = zl;
+    p.valid = (q < g.nxq) && (p.y <= g.H);
+    return p;
+}
+
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void   st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ uchar4 ldf4(const unsigned char* p) { return *reinterpret_cast<const uchar4*>(p); }
+
+// The setBounds epilogue fused into every kernel that writes a field (simulation.cpp:183-246).
+// raw[i] is the value the reference has in the interior cell BEFORE setBounds runs; the face
+// ghosts copy/negate that PRE-zero value (:187-215), then the cell itself is zeroed if it is
+// solid (:219-223) or, for velocity components, touches a solid (:227-245).  Edge/corner ghosts
+// are never written.  In a z-slab the z ghosts exist only on the slabs that own z=1 / z=D.
+__device__ __forceinline__ void fl_store_bounded(const Grid& g, float* __restrict__ out,
+                                                 const unsigned char* __restrict__ flags,
+                                                 int b, int x0, int y, int zl, const float raw[4])
+{
+    const long long c = fl_idx(g, x0, y, zl);
+    const uchar4 f4 = ldf4(flags + c);
+    const unsigned fl[4] = { f4.x, f4.y, f4.z, f4.w };
+    const unsigned zm = fl_zero_mask(b);
+    float v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = (fl[i] & zm) ? 0.0f : raw[i];
+
+    const int nvalid = min(4, g.W - x0 + 1);
+    if (nvalid == 4) {
+        st4(out + c, make_float4(v[0], v[1], v[2], v[3]));
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if (i < nvalid) out[c + i] = v[i];
+    }
+    // x faces (:187-192): x=0 negates only for b==1, x=W+1 is a plain copy (outflow)
+    if (x0 == 1) out[c - 1] = (b == 1) ? -raw[0] : raw[0];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (x0 + i == g.W) out[c + i + 1] = raw[i];
+    // y faces (:196-202)
+    if (y == 1 || y == g.H) {
+        float gy[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) gy[i] = (b == 2) ? -raw[i] : raw[i];
+        if (y == 1) {
+            float* o = out + c - g.pitch;
+            if (nvalid == 4) st4(o, make_float4(gy[0], gy[1], gy[2], gy[3]));
+            else { for (int i = 0; i < nvalid; ++i) o[i] = gy[i]; }
+        }
+        if (y == g.H) {
+            float* o = out + c + g.pitch;
+            if (nvalid == 4) st4(o, make_float4(gy[0], gy[1], gy[2], gy[3]));
+            else { for (int i = 0; i < nvalid; ++i) o[i] = gy[i]; }
+        }
+    }
+    // z faces (:206-215), only on the slab that owns the global boundary plane
+    const int gz = g.zlo + zl - 1;
+    if (gz == 1 || gz == g.D) {
+        float gzv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) gzv[i] = (b == 3) ? -raw[i] : raw[i];
+        if (gz == 1) {
+            float* o = out + c - g.plane;
+            if (nvalid == 4) st4(o, make_float4(gzv[0], gzv[1], gzv[2], gzv[3]));
+            else { for (int i = 0; i < nvalid; ++i) o[i] = gzv[i]; }
+        }
+        if (gz == g.D) {
+            float* o = out + c + g.plane;
+            if (nvalid == 4) st4(o, make_float4(gzv[0], gzv[1], gzv[2], gzv[3]));
+            else { for (int i = 0; i < nvalid; ++i) o[i] = gzv[i]; }
+        }
+    }
+}

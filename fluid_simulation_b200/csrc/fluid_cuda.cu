@@ -1,0 +1,201 @@
+// fluid_cuda.cu -- the C ABI of libfluid_cuda (include/fluid_cuda.h).  One translation unit:
+// kernels live in the kernels_*.cuh / tiled.cuh / wavefront.cuh headers, orchestration in solver.cuh.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -lineinfo (csrc/Makefile).
+// There is no CPU path: without a usable CUDA device every entry point fails.
+#include "solver.cuh"
+#include "tiled.cuh"
+#include "wavefront.cuh"
+#include <cstring>
+#include <new>
+
+thread_local std::string g_fluid_create_error;
+
+static Grid make_grid(int w, int h, int d, int zlo, int dl)
+{
+    Grid g;
+    g.W = w; g.H = h; g.D = d; g.Dl = dl; g.zlo = zlo;
+    g.pitch = (w + 2 + FL_XOFF + 3) / 4 * 4;
+    g.rows = h + 2;
+    g.plane = (long long)g.pitch * g.rows;
+    g.cells = g.plane * (dl + 2);
+    g.nxq = (w + 3) / 4;
+    return g;
+}
+
+static size_t ref_plane_floats(const Grid& g) { return (size_t)(g.W + 2) * g.rows; }
+
+static int alloc_all(fluid_handle* h)
+{
+    const size_t fbytes = (size_t)h->g.cells * sizeof(float);
+    // one zeroed guard row in front of and behind every field keeps the float4 / scalar
+    // neighbour loads of ghost-adjacent quads inside the allocation
+    for (int i = 0; i < FLUID_NFIELDS; ++i) {
+        FL_CUDA(h, cudaMalloc(&h->field[i], fbytes));
+        FL_CUDA(h, cudaMemsetAsync(h->field[i], 0, fbytes, h->stream));   // simulation.cpp:38-43
+    }
+    for (int i = 0; i < 3; ++i) {
+        FL_CUDA(h, cudaMalloc(&h->scratch[i], fbytes));
+        FL_CUDA(h, cudaMemsetAsync(h->scratch[i], 0, fbytes, h->stream));
+    }
+    FL_CUDA(h, cudaMalloc(&h->cflags, (size_t)h->g.cells));
+    FL_CUDA(h, cudaMemsetAsync(h->cflags, 0, (size_t)h->g.cells, h->stream));
+    FL_CUDA(h, cudaMalloc(&h->staging, ref_plane_floats(h->g) * (h->g.Dl + 2) * sizeof(float)));
+    h->n_partial = 148 * 8;
+    FL_CUDA(h, cudaMalloc(&h->d_partial, (size_t)h->n_partial * FL_NSTAT * sizeof(double)));
+    FL_CUDA(h, cudaMalloc(&h->d_out, FL_NSTAT * sizeof(double)));
+    return 0;
+}
+
+static fluid_handle* create_impl(int w, int hgt, int d, int speed, float dt, float diff, float visc,
+                                 int acc, unsigned flags, int rank, int nranks)
+{
+    if (w < 1 || hgt < 1 || d < 1 || acc < 0 || nranks < 1 || rank < 0 || rank >= nranks || nranks > 8 ||
+        d < nranks) {
+        fl_fail(nullptr, FLUID_E_ARG, "fluid_create: bad arguments (w=%d h=%d d=%d acc=%d rank=%d/%d)",
+                w, hgt, d, acc, rank, nranks);
+        return nullptr;
+    }
+    if ((long long)(w + 2) * (hgt + 2) * (d + 2) > 2147483647LL) {
+        fl_fail(nullptr, FLUID_E_ARG, "fluid_create: padded cell count exceeds int range (simulation.h:13)");
+        return nullptr;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        fl_fail(nullptr, FLUID_E_CUDA, "fluid_create: no CUDA device (%s); libfluid_cuda has no CPU fallback",
+                cudaGetErrorString(e));
+        return nullptr;
+    }
+    fluid_handle* h = new (std::nothrow) fluid_handle();
+    if (!h) { fl_fail(nullptr, FLUID_E_NOMEM, "fluid_create: out of host memory"); return nullptr; }
+    cudaGetDevice(&h->device);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess) {
+        h->sm_count = prop.multiProcessorCount;
+        if (prop.major < 10) {
+            fl_fail(nullptr, FLUID_E_CUDA, "fluid_create: device sm_%d%d is not Blackwell (built for sm_100a only)",
+                    prop.major, prop.minor);
+            delete h; return nullptr;
+        }
+    }
+    // equal z-slabs, remainder planes to the low ranks
+    int base = d / nranks, rem = d % nranks;
+    int dl = base + (rank < rem ? 1 : 0);
+    int zlo = 1 + rank * base + (rank < rem ? rank : rem);
+    h->g = make_grid(w, hgt, d, zlo, dl);
+    h->speed = speed; h->dt = dt; h->diff = diff; h->visc = visc; h->acc = acc; h->flags = flags;
+    h->rank = rank; h->nranks = nranks;
+    bool ok = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&h->dump_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&h->halo_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_frame_packed, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_frame_done, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_a, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_b, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreate(&h->ev_t0) == cudaSuccess && cudaEventCreate(&h->ev_t1) == cudaSuccess;
+    if (!ok || alloc_all(h) != 0 || cudaStreamSynchronize(h->stream) != cudaSuccess) {
+        std::string msg = h->err.empty() ? std::string("stream/event creation failed: ") +
+                                           cudaGetErrorString(cudaGetLastError()) : h->err;
+        fluid_destroy(h);
+        fl_fail(nullptr, FLUID_E_CUDA, "fluid_create: %s", msg.c_str());
+        return nullptr;
+    }
+    return h;
+}
+
+extern "C" {
+
+const char* fluid_version(void)
+{
+    return "libfluid_cuda 0.1 (sm_100a, --fmad=false, built " __DATE__ ")";
+}
+
+fluid_handle* fluid_create(int w, int h, int d, int speed, float dt, float diff, float visc,
+                           int acc, unsigned flags)
+{
+    return create_impl(w, h, d, speed, dt, diff, visc, acc, flags, 0, 1);
+}
+
+fluid_handle* fluid_create_slab(int w, int h, int d, int speed, float dt, float diff, float visc,
+                                int acc, unsigned flags, int rank, int nranks)
+{
+    return create_impl(w, h, d, speed, dt, diff, visc, acc, flags, rank, nranks);
+}
+
+void fluid_destroy(fluid_handle* h)
+{
+    if (!h) return;
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->dump_stream) cudaStreamSynchronize(h->dump_stream);
+    fl_tiled_release(h);
+    fl_comm_release(h);
+    for (int i = 0; i < FLUID_NFIELDS; ++i) cudaFree(h->field[i]);
+    for (int i = 0; i < 3; ++i) cudaFree(h->scratch[i]);
+    for (int i = 0; i < 5; ++i) cudaFree(h->frame_staging[i]);
+    cudaFree(h->cflags); cudaFree(h->staging); cudaFree(h->d_partial); cudaFree(h->d_out);
+    cudaFree(h->d_xyz); cudaFree(h->d_val);
+    if (h->ev_frame_packed) cudaEventDestroy(h->ev_frame_packed);
+    if (h->ev_frame_done) cudaEventDestroy(h->ev_frame_done);
+    if (h->ev_a) cudaEventDestroy(h->ev_a);
+    if (h->ev_b) cudaEventDestroy(h->ev_b);
+    if (h->ev_t0) cudaEventDestroy(h->ev_t0);
+    if (h->ev_t1) cudaEventDestroy(h->ev_t1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->dump_stream) cudaStreamDestroy(h->dump_stream);
+    if (h->halo_stream) cudaStreamDestroy(h->halo_stream);
+    delete h;
+}
+
+const char* fluid_last_error(fluid_handle* h) { return h ? h->err.c_str() : g_fluid_create_error.c_str(); }
+
+int fluid_set_acc(fluid_handle* h, int acc)
+{
+    if (!h || acc < 0) return fl_fail(h, FLUID_E_ARG, "fluid_set_acc: bad argument");
+    h->acc = acc;
+    return 0;
+}
+
+int fluid_get_dims(fluid_handle* h, int* w, int* hh, int* d, int* z_lo, int* d_local)
+{
+    if (!h) return FLUID_E_ARG;
+    if (w) *w = h->g.W; if (hh) *hh = h->g.H; if (d) *d = h->g.D;
+    if (z_lo) *z_lo = h->g.zlo; if (d_local) *d_local = h->g.Dl;
+    return 0;
+}
+
+int fluid_sync(fluid_handle* h)
+{
+    if (!h) return FLUID_E_ARG;
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+long long fluid_launch_count(fluid_handle* h) { return h ? h->launches : 0; }
+
+void* fluid_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void fluid_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int fluid_timer_start(fluid_handle* h)
+{
+    if (!h) return FLUID_E_ARG;
+    FL_CUDA(h, cudaEventRecord(h->ev_t0, h->stream));
+    return 0;
+}
+int fluid_timer_stop(fluid_handle* h, float* ms)
+{
+    if (!h || !ms) return FLUID_E_ARG;
+    FL_CUDA(h, cudaEventRecord(h->ev_t1, h->stream));
+    FL_CUDA(h, cudaEventSynchronize(h->ev_t1));
+    FL_CUDA(h, cudaEventElapsedTime(ms, h->ev_t0, h->ev_t1));
+    return 0;
+}
+
+}  // extern "C"
+
+#include "api_io.inl"
+#include "api_ops.inl"

@@ -1,0 +1,138 @@
+// kernels_basic.cuh -- layout conversion, flag volume, inflow, standalone setBounds, sparse mutators.
+#pragma once
+#include "common.cuh"
+
+// ---- reference layout <-> pitched HBM layout (host boundary only) ----------------------------
+// host volume is the GLOBAL padded array; a slab moves local planes zl=0..Dl+1 <-> global z = zlo-1+zl.
+// `staging` holds exactly those planes in reference row order: (Dl+2) * (H+2) * (W+2) floats.
+__global__ void k_unpack(Grid g, const float* __restrict__ staging, float* __restrict__ field)
+{
+    const int Wp = g.W + 2;
+    long long n = (long long)Wp * g.rows * (g.Dl + 2);
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n;
+         t += (long long)gridDim.x * blockDim.x) {
+        int x = (int)(t % Wp);
+        long long r = t / Wp;
+        int y = (int)(r % g.rows);
+        int zl = (int)(r / g.rows);
+        field[fl_idx(g, x, y, zl)] = staging[t];
+    }
+}
+
+__global__ void k_pack(Grid g, const float* __restrict__ field, float* __restrict__ staging)
+{
+    const int Wp = g.W + 2;
+    long long n = (long long)Wp * g.rows * (g.Dl + 2);
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n;
+         t += (long long)gridDim.x * blockDim.x) {
+        int x = (int)(t % Wp);
+        long long r = t / Wp;
+        int y = (int)(r % g.rows);
+        int zl = (int)(r / g.rows);
+        staging[t] = field[fl_idx(g, x, y, zl)];
+    }
+}
+
+// ---- flag volume (once per obstacle upload) ---------------------------------------------------
+// Encodes exactly the obs tests the reference performs: `== 1.0f` for solid, `== 0.0f` plus the
+// 1..dim range test for "open" neighbours (simulation.cpp:222, 232-238, 307-312, 329-355).
+// obs has valid halo planes in slab mode, so the +-z tests see the neighbouring slab's mask.
+__global__ void k_build_flags(Grid g, const float* __restrict__ obs, unsigned char* __restrict__ flags)
+{
+    long long n = g.cells;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n;
+         t += (long long)gridDim.x * blockDim.x) {
+        long long r = t;
+        int zl = (int)(r / g.plane); r -= (long long)zl * g.plane;
+        int y = (int)(r / g.pitch);
+        int x = (int)(r - (long long)y * g.pitch) - FL_XOFF;
+        int gz = g.zlo + zl - 1;
+        unsigned f = 0;
+        if (x >= 1 && x <= g.W && y >= 1 && y <= g.H && zl >= 1 && zl <= g.Dl) {
+            const float o = obs[t];
+            const bool inxp = x + 1 <= g.W, inxm = x - 1 >= 1, inyp = y + 1 <= g.H, inym = y - 1 >= 1;
+            const bool inzp = gz + 1 <= g.D, inzm = gz - 1 >= 1;
+            const float oxp = obs[t + 1], oxm = obs[t - 1];
+            const float oyp = obs[t + g.pitch], oym = obs[t - g.pitch];
+            const float ozp = obs[t + g.plane], ozm = obs[t - g.plane];
+            if (o == 1.0f) f |= FL_SOLID;
+            else if ((inxp && oxp == 1.0f) || (inxm && oxm == 1.0f) || (inyp && oyp == 1.0f) ||
+                     (inym && oym == 1.0f) || (inzp && ozp == 1.0f) || (inzm && ozm == 1.0f))
+                f |= FL_NOSLIP;
+            if (inxp && oxp == 0.0f) f |= FL_OPEN_XP;
+            if (inxm && oxm == 0.0f) f |= FL_OPEN_XM;
+            if (inyp && oyp == 0.0f) f |= FL_OPEN_YP;
+            if (inym && oym == 0.0f) f |= FL_OPEN_YM;
+            if (inzp && ozp == 0.0f) f |= FL_OPEN_ZP;
+            if (inzm && ozm == 0.0f) f |= FL_OPEN_ZM;
+        }
+        flags[t] = (unsigned char)f;
+    }
+}
+
+// ---- inlet on the x = 1 face (no setBounds follows in the reference) --------------------------
+// run(): dens(1,j,k) += 0.001f            simulation.cpp:65-67
+__global__ void k_inflow_density(Grid g, float* __restrict__ dens, float amount)
+{
+    int y = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+    int zl = 1 + blockIdx.y;
+    if (y <= g.H) dens[fl_idx(g, 1, y, zl)] += amount;
+}
+
+// step(): v(1,j,k) = (speed, 0, 0)        simulation.cpp:103-105
+__global__ void k_inflow_velocity(Grid g, float* __restrict__ vx, float* __restrict__ vy,
+                                  float* __restrict__ vz, float speed)
+{
+    int y = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+    int zl = 1 + blockIdx.y;
+    if (y <= g.H) {
+        long long c = fl_idx(g, 1, y, zl);
+        vx[c] = speed; vy[c] = 0.0f; vz[c] = 0.0f;
+    }
+}
+
+// ---- standalone setBounds(b, field), simulation.cpp:183-246 -----------------------------------
+// One thread owns each interior quad: it reads the stored (pre-zero) value once, derives the
+// ghosts from that register copy, then writes the masked value -- no inter-thread ordering needed.
+__global__ void __launch_bounds__(256) k_set_bounds(Grid g, float* __restrict__ field,
+                                                    const unsigned char* __restrict__ flags, int b)
+{
+    QuadPos p = fl_quad_pos(g, 1 + blockIdx.z);
+    if (!p.valid) return;
+    float4 c = ld4(field + fl_idx(g, p.x0, p.y, p.zl));
+    float raw[4] = { c.x, c.y, c.z, c.w };
+    fl_store_bounded(g, field, flags, b, p.x0, p.y, p.zl, raw);
+}
+
+// ---- sparse mutators (addObstacle / addDensity / setVelocity, simulation.cpp:155-178) --------
+// xyz are GLOBAL 0..dim+1 coordinates; cells outside this slab's planes (incl. halos) are skipped.
+__global__ void k_add_density(Grid g, float* __restrict__ dens, int n, const int* __restrict__ xyz,
+                              const float* __restrict__ amount)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    int zl = xyz[3 * t + 2] - g.zlo + 1;
+    if (zl < 0 || zl > g.Dl + 1) return;
+    atomicAdd(&dens[fl_idx(g, xyz[3 * t], xyz[3 * t + 1], zl)], amount[t]);
+}
+
+__global__ void k_set_velocity(Grid g, float* __restrict__ vx, float* __restrict__ vy,
+                               float* __restrict__ vz, int n, const int* __restrict__ xyz,
+                               const float* __restrict__ v)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    int zl = xyz[3 * t + 2] - g.zlo + 1;
+    if (zl < 0 || zl > g.Dl + 1) return;
+    long long c = fl_idx(g, xyz[3 * t], xyz[3 * t + 1], zl);
+    vx[c] = v[3 * t]; vy[c] = v[3 * t + 1]; vz[c] = v[3 * t + 2];
+}
+
+__global__ void k_add_obstacles(Grid g, float* __restrict__ obs, int n, const int* __restrict__ xyz)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    int zl = xyz[3 * t + 2] - g.zlo + 1;
+    if (zl < 0 || zl > g.Dl + 1) return;
+    obs[fl_idx(g, xyz[3 * t], xyz[3 * t + 1], zl)] = 1.0f;
+}

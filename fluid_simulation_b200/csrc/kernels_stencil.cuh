@@ -1,0 +1,226 @@
+// kernels_stencil.cuh -- simple global-memory versions of the stencil kernels (one thread = one
+// x-quad, float4 rows, L1/L2 provide the neighbour reuse).  They are the reference-exact
+// baseline that the TMA/shared-memory tiled sweeps (kernels_tiled.cuh) are A/B-checked against,
+// and they handle every grid shape.  All arithmetic is compiled with --fmad=false and keeps the
+// reference's operand order so results are bit-identical to the CPU code.
+#pragma once
+#include "common.cuh"
+
+// the 7-point update of linearSolver (simulation.cpp:263-269); neighbour sum strictly left to
+// right: x+1, x-1, y+1, y-1, z+1, z-1
+__device__ __forceinline__ float fl_relax(float rhs, float a, float c_recip, float xp, float xm,
+                                          float yp, float ym, float zp, float zm)
+{
+    return (rhs + a * (((((xp + xm) + yp) + ym) + zp) + zm)) * c_recip;
+}
+
+struct Quad7 { float c[4], xm, xp, yp[4], ym[4], zp[4], zm[4]; };
+
+__device__ __forceinline__ void fl_load_quad7(const Grid& g, const float* __restrict__ f,
+                                              long long c, Quad7& q)
+{
+    float4 v = ld4(f + c);            q.c[0] = v.x;  q.c[1] = v.y;  q.c[2] = v.z;  q.c[3] = v.w;
+    q.xm = f[c - 1];                  q.xp = f[c + 4];
+    v = ld4(f + c + g.pitch);         q.yp[0] = v.x; q.yp[1] = v.y; q.yp[2] = v.z; q.yp[3] = v.w;
+    v = ld4(f + c - g.pitch);         q.ym[0] = v.x; q.ym[1] = v.y; q.ym[2] = v.z; q.ym[3] = v.w;
+    v = ld4(f + c + g.plane);         q.zp[0] = v.x; q.zp[1] = v.y; q.zp[2] = v.z; q.zp[3] = v.w;
+    v = ld4(f + c - g.plane);         q.zm[0] = v.x; q.zm[1] = v.y; q.zm[2] = v.z; q.zm[3] = v.w;
+}
+
+// ---- Jacobi sweep + fused setBounds: dst = bounds(relax(src)), simulation.cpp:259-271 --------
+// Batched over `nb` fields (blockIdx.z = batch * Dl + plane) so the three velocity diffusions,
+// which share a and c (simulation.cpp:282-283), go out as one launch.
+struct SweepBatch { const float* src[3]; const float* rhs[3]; float* dst[3]; int b[3]; };
+
+__global__ void __launch_bounds__(256) k_sweep_jacobi(Grid g, SweepBatch sb,
+                                                      const unsigned char* __restrict__ flags,
+                                                      float a, float c_recip)
+{
+    const int batch = blockIdx.z / g.Dl;
+    QuadPos p = fl_quad_pos(g, 1 + blockIdx.z % g.Dl);
+    if (!p.valid) return;
+    const float* __restrict__ src = sb.src[batch];
+    const float* __restrict__ rhs = sb.rhs[batch];
+    const long long c = fl_idx(g, p.x0, p.y, p.zl);
+    Quad7 q; fl_load_quad7(g, src, c, q);
+    float4 r4 = ld4(rhs + c);
+    const float r[4] = { r4.x, r4.y, r4.z, r4.w };
+    float raw[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float xp = (i == 3) ? q.xp : q.c[i + 1];
+        float xm = (i == 0) ? q.xm : q.c[i - 1];
+        raw[i] = fl_relax(r[i], a, c_recip, xp, xm, q.yp[i], q.ym[i], q.zp[i], q.zm[i]);
+    }
+    fl_store_bounded(g, sb.dst[batch], flags, sb.b[batch], p.x0, p.y, p.zl, raw);
+}
+
+// ---- red-black half sweep, in place, no bounds (they run after the black half) ---------------
+// colour 0 = cells with (i+j+l) even, global coordinates.  Only cells of `colour` change; the
+// other two lanes of the quad are written back unchanged (nobody else writes them in this pass).
+__global__ void __launch_bounds__(256) k_sweep_rb_half(Grid g, SweepBatch sb, float a, float c_recip,
+                                                       int colour)
+{
+    const int batch = blockIdx.z / g.Dl;
+    QuadPos p = fl_quad_pos(g, 1 + blockIdx.z % g.Dl);
+    if (!p.valid) return;
+    float* __restrict__ f = sb.dst[batch];
+    const float* __restrict__ rhs = sb.rhs[batch];
+    const long long c = fl_idx(g, p.x0, p.y, p.zl);
+    Quad7 q; fl_load_quad7(g, f, c, q);
+    float4 r4 = ld4(rhs + c);
+    const float r[4] = { r4.x, r4.y, r4.z, r4.w };
+    const int gz = g.zlo + p.zl - 1;
+    const int par0 = (p.x0 + p.y + gz) & 1;       // parity of lane 0
+    float out[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float xp = (i == 3) ? q.xp : q.c[i + 1];
+        float xm = (i == 0) ? q.xm : q.c[i - 1];
+        float v = fl_relax(r[i], a, c_recip, xp, xm, q.yp[i], q.ym[i], q.zp[i], q.zm[i]);
+        out[i] = (((par0 + i) & 1) == colour) ? v : q.c[i];
+    }
+    const int nvalid = min(4, g.W - p.x0 + 1);
+    if (nvalid == 4) st4(f + c, make_float4(out[0], out[1], out[2], out[3]));
+    else for (int i = 0; i < nvalid; ++i) f[c + i] = out[i];
+}
+
+// ---- project part 1: divergence, p = 0, setBounds(0,div), setBounds(0,p) (:295-319) ----------
+__global__ void __launch_bounds__(256) k_divergence(Grid g, const float* __restrict__ vx,
+                                                    const float* __restrict__ vy,
+                                                    const float* __restrict__ vz,
+                                                    const unsigned char* __restrict__ flags,
+                                                    float* __restrict__ div, float* __restrict__ p,
+                                                    float h)
+{
+    QuadPos q = fl_quad_pos(g, 1 + blockIdx.z);
+    if (!q.valid) return;
+    const long long c = fl_idx(g, q.x0, q.y, q.zl);
+    const uchar4 f4 = ldf4(flags + c);
+    const unsigned fl[4] = { f4.x, f4.y, f4.z, f4.w };
+    const float4 xc = ld4(vx + c);
+    const float vxq[6] = { vx[c - 1], xc.x, xc.y, xc.z, xc.w, vx[c + 4] };
+    const float4 a = ld4(vy + c + g.pitch), bq = ld4(vy + c - g.pitch);
+    const float4 cz = ld4(vz + c + g.plane), dz = ld4(vz + c - g.plane);
+    const float yp[4] = { a.x, a.y, a.z, a.w }, ym[4] = { bq.x, bq.y, bq.z, bq.w };
+    const float zp[4] = { cz.x, cz.y, cz.z, cz.w }, zm[4] = { dz.x, dz.y, dz.z, dz.w };
+    float raw[4], zero[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float s = 0.0f;                                           // :306-312, same order
+        if (fl[i] & FL_OPEN_XP) s += vxq[i + 2];
+        if (fl[i] & FL_OPEN_XM) s -= vxq[i];
+        if (fl[i] & FL_OPEN_YP) s += yp[i];
+        if (fl[i] & FL_OPEN_YM) s -= ym[i];
+        if (fl[i] & FL_OPEN_ZP) s += zp[i];
+        if (fl[i] & FL_OPEN_ZM) s -= zm[i];
+        raw[i] = (fl[i] & FL_SOLID) ? 0.0f : -0.5f * h * s;       // :301-305, :314
+    }
+    fl_store_bounded(g, div, flags, 0, q.x0, q.y, q.zl, raw);
+    fl_store_bounded(g, p, flags, 0, q.x0, q.y, q.zl, zero);
+}
+
+// one-sided / central pressure difference (simulation.cpp:328-336 and the y, z copies)
+__device__ __forceinline__ float fl_axis_grad(bool po, bool mo, float pp, float pc, float pm, float h)
+{
+    if (po && mo) return (pp - pm) / (2.0f * h);
+    if (po)       return (pp - pc) / h;
+    if (mo)       return (pc - pm) / h;
+    return 0.0f;
+}
+
+// ---- project part 3: v -= grad p on fluid cells, then setBounds(1..3) (:322-361) -------------
+__global__ void __launch_bounds__(256) k_gradient(Grid g, const float* __restrict__ p,
+                                                  const unsigned char* __restrict__ flags,
+                                                  float* __restrict__ vx, float* __restrict__ vy,
+                                                  float* __restrict__ vz, float h)
+{
+    QuadPos qp = fl_quad_pos(g, 1 + blockIdx.z);
+    if (!qp.valid) return;
+    const long long c = fl_idx(g, qp.x0, qp.y, qp.zl);
+    const uchar4 f4 = ldf4(flags + c);
+    const unsigned fl[4] = { f4.x, f4.y, f4.z, f4.w };
+    Quad7 q; fl_load_quad7(g, p, c, q);
+    const float4 ax = ld4(vx + c), ay = ld4(vy + c), az = ld4(vz + c);
+    float rx[4] = { ax.x, ax.y, ax.z, ax.w }, ry[4] = { ay.x, ay.y, ay.z, ay.w },
+          rz[4] = { az.x, az.y, az.z, az.w };
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (fl[i] & FL_SOLID) continue;                           // :326 solids keep their value
+        float pxp = (i == 3) ? q.xp : q.c[i + 1];
+        float pxm = (i == 0) ? q.xm : q.c[i - 1];
+        rx[i] -= fl_axis_grad(fl[i] & FL_OPEN_XP, fl[i] & FL_OPEN_XM, pxp, q.c[i], pxm, h);
+        ry[i] -= fl_axis_grad(fl[i] & FL_OPEN_YP, fl[i] & FL_OPEN_YM, q.yp[i], q.c[i], q.ym[i], h);
+        rz[i] -= fl_axis_grad(fl[i] & FL_OPEN_ZP, fl[i] & FL_OPEN_ZM, q.zp[i], q.c[i], q.zm[i], h);
+    }
+    fl_store_bounded(g, vx, flags, 1, qp.x0, qp.y, qp.zl, rx);
+    fl_store_bounded(g, vy, flags, 2, qp.x0, qp.y, qp.zl, ry);
+    fl_store_bounded(g, vz, flags, 3, qp.x0, qp.y, qp.zl, rz);
+}
+
+// ---- advect(b, field, prev) + setBounds (simulation.cpp:367-424) -----------------------------
+// `src` is the gather source (prev_field) as an array of per-slab base pointers: src_slab[r]
+// holds global planes src_zlo[r]-1 .. ; on one GPU there is a single entry.  The own-cell
+// velocity of component b comes from prev (:380-382), the other two from the current fields.
+struct GatherSrc { const float* base[8]; int zlo[8]; int dl[8]; int n; };
+
+__device__ __forceinline__ float fl_gather(const Grid& g, const GatherSrc& s, int x, int y, int gz)
+{
+    // global plane gz lives on the slab with zlo <= gz < zlo+dl (ghost planes 0 / D+1 on the ends)
+    int r = 0;
+#pragma unroll 1
+    for (int k = 0; k < s.n - 1; ++k) if (gz >= s.zlo[k] + s.dl[k]) r = k + 1;
+    return __ldg(s.base[r] + fl_idx(g, x, y, gz - s.zlo[r] + 1));
+}
+
+__device__ __forceinline__ float fl_clamp(float v, float lo, float hi)       // std::clamp
+{
+    return (v < lo) ? lo : (hi < v) ? hi : v;
+}
+
+__global__ void __launch_bounds__(256) k_advect(Grid g, int b, float* __restrict__ field,
+                                                const float* __restrict__ prev_local, GatherSrc src,
+                                                const float* __restrict__ vxf,
+                                                const float* __restrict__ vyf,
+                                                const float* __restrict__ vzf,
+                                                const unsigned char* __restrict__ flags, float dt)
+{
+    QuadPos qp = fl_quad_pos(g, 1 + blockIdx.z);
+    if (!qp.valid) return;
+    const long long c = fl_idx(g, qp.x0, qp.y, qp.zl);
+    const uchar4 f4 = ldf4(flags + c);
+    const unsigned fl[4] = { f4.x, f4.y, f4.z, f4.w };
+    const float4 ax = ld4((b == 1 ? prev_local : vxf) + c);
+    const float4 ay = ld4((b == 2 ? prev_local : vyf) + c);
+    const float4 az = ld4((b == 3 ? prev_local : vzf) + c);
+    const float vx[4] = { ax.x, ax.y, ax.z, ax.w }, vy[4] = { ay.x, ay.y, ay.z, ay.w },
+                vz[4] = { az.x, az.y, az.z, az.w };
+    const int gz = g.zlo + qp.zl - 1;
+    const float fW = (float)g.W, fH = (float)g.H, fD = (float)g.D;
+    float raw[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        raw[i] = 0.0f;
+        if ((fl[i] & FL_SOLID) || qp.x0 + i > g.W) continue;                 // :375-378
+        float xb = (float)(qp.x0 + i) - dt * fW * vx[i];                     // :384-386
+        float yb = (float)qp.y - dt * fH * vy[i];
+        float zb = (float)gz - dt * fD * vz[i];
+        xb = fl_clamp(xb, 0.5f, fW + 0.5f);                                  // :388-390
+        yb = fl_clamp(yb, 0.5f, fH + 0.5f);
+        zb = fl_clamp(zb, 0.5f, fD + 0.5f);
+        const int i0 = (int)floorf(xb), j0 = (int)floorf(yb), k0 = (int)floorf(zb);   // :392-397
+        const float sx = xb - (float)i0, sy = yb - (float)j0, sz = zb - (float)k0;    // :399-401
+        const float c000 = fl_gather(g, src, i0, j0, k0),     c100 = fl_gather(g, src, i0 + 1, j0, k0);
+        const float c010 = fl_gather(g, src, i0, j0 + 1, k0), c110 = fl_gather(g, src, i0 + 1, j0 + 1, k0);
+        const float c001 = fl_gather(g, src, i0, j0, k0 + 1),     c101 = fl_gather(g, src, i0 + 1, j0, k0 + 1);
+        const float c011 = fl_gather(g, src, i0, j0 + 1, k0 + 1), c111 = fl_gather(g, src, i0 + 1, j0 + 1, k0 + 1);
+        const float c00 = c000 * (1.0f - sx) + c100 * sx;                    // :412-415
+        const float c01 = c001 * (1.0f - sx) + c101 * sx;
+        const float c10 = c010 * (1.0f - sx) + c110 * sx;
+        const float c11 = c011 * (1.0f - sx) + c111 * sx;
+        const float c0 = c00 * (1.0f - sy) + c10 * sy;                       // :417-418
+        const float c1 = c01 * (1.0f - sy) + c11 * sy;
+        raw[i] = c0 * (1.0f - sz) + c1 * sz;                                 // :420
+    }
+    fl_store_bounded(g, field, flags, b, qp.x0, qp.y, qp.zl, raw);
+}

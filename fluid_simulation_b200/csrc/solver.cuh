@@ -1,0 +1,210 @@
+// solver.cuh -- host-side orchestration of the per-timestep hot path: the launch sequences that
+// replace Simulation::linearSolver / diffuse / project / advect / step (simulation.cpp:96-424).
+// Every "omp barrier" / loop nest of the reference is a kernel boundary on h->stream.
+#pragma once
+#include "handle.cuh"
+#include "kernels_basic.cuh"
+#include "kernels_stencil.cuh"
+#include "kernels_reduce.cuh"
+#include <math.h>
+
+int fl_halo_exchange(fluid_handle* h, int n, float* const* fields);      // fluid_cuda.cu (slab mode)
+int fl_lex_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
+                 float a, float c);                                      // wavefront.cuh
+int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
+                   float a, float c, bool* handled);                     // tiled.cuh
+void fl_tiled_release(fluid_handle* h);                                  // tiled.cuh
+void fl_comm_release(fluid_handle* h);                                   // api_ops.inl
+
+static inline int fl_rebuild_flags(fluid_handle* h)
+{
+    if (!h->flags_dirty) return 0;
+    k_build_flags<<<fl_grid_1d(h->g.cells), 256, 0, h->stream>>>(h->g, h->field[FLUID_OBS], h->cflags);
+    FL_CHECK_LAUNCH(h);
+    h->flags_dirty = false;
+    return 0;
+}
+
+// host scalars with the reference's exact float expressions (compiled without contraction)
+static inline float fl_diffuse_a(const fluid_handle* h)
+{
+    // simulation.cpp:282: dt * diff * width * height * depth, left to right, ints -> float
+    volatile float a = h->dt * h->diff;
+    a = a * (float)h->g.W; a = a * (float)h->g.H; a = a * (float)h->g.D;
+    return a;
+}
+static inline float fl_project_h(const fluid_handle* h)
+{
+    // simulation.cpp:295: 1.0f / std::cbrt(float(int product))
+    return 1.0f / cbrtf((float)(h->g.W * h->g.H * h->g.D));
+}
+
+static inline int fl_set_bounds(fluid_handle* h, int b, int fid)
+{
+    if (int e = fl_rebuild_flags(h)) return e;
+    QuadLaunch q = fl_quad_launch(h->g, h->g.Dl);
+    k_set_bounds<<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[fid], h->cflags, b);
+    FL_CHECK_LAUNCH(h);
+    return 0;
+}
+
+// linearSolver(b, field, prev, a, c) for up to three fields that share a and c
+// (simulation.cpp:251-273): acc sweeps, setBounds after each.
+static inline int fl_lin_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
+                               float a, float c)
+{
+    if (int e = fl_rebuild_flags(h)) return e;
+    if (h->acc <= 0) return 0;
+    const unsigned solver = h->flags & FLUID_SOLVER_MASK;
+    if (solver == FLUID_SOLVER_LEX) return fl_lex_solve(h, nb, b, fid, pid, a, c);
+    if (!(h->flags & FLUID_NO_TILED)) {
+        bool handled = false;
+        if (int e = fl_tiled_solve(h, nb, b, fid, pid, a, c, &handled)) return e;
+        if (handled) return 0;
+    }
+    const float c_recip = 1.0f / c;                                       // simulation.cpp:257
+    const Grid& g = h->g;
+    QuadLaunch q = fl_quad_launch(g, g.Dl * nb);
+    SweepBatch sb;
+    float* cur[3]; float* alt[3];
+    for (int i = 0; i < nb; ++i) {
+        cur[i] = h->field[fid[i]]; alt[i] = h->scratch[i];
+        sb.rhs[i] = h->field[pid[i]]; sb.b[i] = b[i];
+    }
+    for (int k = 0; k < h->acc; ++k) {                                    // simulation.cpp:258
+        if (solver == FLUID_SOLVER_JACOBI) {
+            for (int i = 0; i < nb; ++i) { sb.src[i] = cur[i]; sb.dst[i] = alt[i]; }
+            k_sweep_jacobi<<<q.grid, q.block, 0, h->stream>>>(g, sb, h->cflags, a, c_recip);
+            FL_CHECK_LAUNCH(h);
+            for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
+        } else {  // red-black, in place: colour 0, colour 1, then setBounds
+            for (int i = 0; i < nb; ++i) { sb.src[i] = cur[i]; sb.dst[i] = cur[i]; }
+            for (int colour = 0; colour < 2; ++colour) {
+                k_sweep_rb_half<<<q.grid, q.block, 0, h->stream>>>(g, sb, a, c_recip, colour);
+                FL_CHECK_LAUNCH(h);
+            }
+            QuadLaunch qb = fl_quad_launch(g, g.Dl);
+            for (int i = 0; i < nb; ++i) {
+                k_set_bounds<<<qb.grid, qb.block, 0, h->stream>>>(g, cur[i], h->cflags, b[i]);
+                FL_CHECK_LAUNCH(h);
+            }
+        }
+        if (h->nranks > 1) if (int e = fl_halo_exchange(h, nb, cur)) return e;
+    }
+    // Jacobi ping-pong: the result may live in the scratch buffer -> swap ownership, no copy
+    for (int i = 0; i < nb; ++i) {
+        if (cur[i] != h->field[fid[i]]) { h->scratch[i] = h->field[fid[i]]; h->field[fid[i]] = cur[i]; }
+    }
+    return 0;
+}
+
+static inline int fl_diffuse(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid)
+{
+    const float a = fl_diffuse_a(h);                                      // simulation.cpp:282
+    volatile float c = 6.0f * a; c = 1.0f + c;                            // :283, no contraction
+    return fl_lin_solve(h, nb, b, fid, pid, a, c);
+}
+
+static inline int fl_divergence(fluid_handle* h)
+{
+    if (int e = fl_rebuild_flags(h)) return e;
+    if (h->nranks > 1) { float* f[1] = { h->field[FLUID_VZ] }; if (int e = fl_halo_exchange(h, 1, f)) return e; }
+    QuadLaunch q = fl_quad_launch(h->g, h->g.Dl);
+    k_divergence<<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY],
+                                                    h->field[FLUID_VZ], h->cflags,
+                                                    h->field[FLUID_DIVERGENCE], h->field[FLUID_PRESSURE],
+                                                    fl_project_h(h));
+    FL_CHECK_LAUNCH(h);
+    if (h->nranks > 1) { float* f[1] = { h->field[FLUID_PRESSURE] }; if (int e = fl_halo_exchange(h, 1, f)) return e; }
+    return 0;
+}
+
+static inline int fl_gradient(fluid_handle* h)
+{
+    if (int e = fl_rebuild_flags(h)) return e;
+    QuadLaunch q = fl_quad_launch(h->g, h->g.Dl);
+    k_gradient<<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags,
+                                                  h->field[FLUID_VX], h->field[FLUID_VY],
+                                                  h->field[FLUID_VZ], fl_project_h(h));
+    FL_CHECK_LAUNCH(h);
+    return 0;
+}
+
+static inline int fl_project(fluid_handle* h)                             // simulation.cpp:289-362
+{
+    if (int e = fl_divergence(h)) return e;
+    const int b = 0, f = FLUID_PRESSURE, p = FLUID_DIVERGENCE;
+    if (int e = fl_lin_solve(h, 1, &b, &f, &p, 1.0f, 6.0f)) return e;     // :320
+    return fl_gradient(h);
+}
+
+int fl_gather_sources(fluid_handle* h, int prev_id, GatherSrc* out);      // fluid_cuda.cu
+
+static inline int fl_advect(fluid_handle* h, int b, int fid, int pid)     // simulation.cpp:367-424
+{
+    if (int e = fl_rebuild_flags(h)) return e;
+    GatherSrc src;
+    if (int e = fl_gather_sources(h, pid, &src)) return e;
+    QuadLaunch q = fl_quad_launch(h->g, h->g.Dl);
+    k_advect<<<q.grid, q.block, 0, h->stream>>>(h->g, b, h->field[fid], h->field[pid], src,
+                                                h->field[FLUID_VX], h->field[FLUID_VY],
+                                                h->field[FLUID_VZ], h->cflags, h->dt);
+    FL_CHECK_LAUNCH(h);
+    return 0;
+}
+
+static inline int fl_inflow_density(fluid_handle* h)                      // simulation.cpp:65-67
+{
+    dim3 grid((h->g.H + 127) / 128, h->g.Dl);
+    k_inflow_density<<<grid, 128, 0, h->stream>>>(h->g, h->field[FLUID_DENS], 0.001f);
+    FL_CHECK_LAUNCH(h);
+    return 0;
+}
+
+static inline int fl_inflow_velocity(fluid_handle* h)                     // simulation.cpp:103-105
+{
+    dim3 grid((h->g.H + 127) / 128, h->g.Dl);
+    k_inflow_velocity<<<grid, 128, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY],
+                                                   h->field[FLUID_VZ], (float)h->speed);
+    FL_CHECK_LAUNCH(h);
+    return 0;
+}
+
+static inline int fl_copy_field(fluid_handle* h, int dst, int src)
+{
+    FL_CUDA(h, cudaMemcpyAsync(h->field[dst], h->field[src], (size_t)h->g.cells * sizeof(float),
+                               cudaMemcpyDeviceToDevice, h->stream));
+    return 0;
+}
+
+// Simulation::step() without the frame write (simulation.cpp:96-138)
+static inline int fl_step_only(fluid_handle* h)
+{
+    if (int e = fl_inflow_velocity(h)) return e;                          // :103-105
+    if (int e = fl_copy_field(h, FLUID_VX_PREV, FLUID_VX)) return e;      // :108-110
+    if (int e = fl_copy_field(h, FLUID_VY_PREV, FLUID_VY)) return e;
+    if (int e = fl_copy_field(h, FLUID_VZ_PREV, FLUID_VZ)) return e;
+    {   // :115-117 the three velocity diffusions share a and c -> one batched launch per sweep
+        const int b[3] = { 1, 2, 3 }, f[3] = { FLUID_VX, FLUID_VY, FLUID_VZ },
+                  p[3] = { FLUID_VX_PREV, FLUID_VY_PREV, FLUID_VZ_PREV };
+        if (int e = fl_diffuse(h, 3, b, f, p)) return e;
+    }
+    if (int e = fl_project(h)) return e;                                  // :120
+    if (int e = fl_advect(h, 1, FLUID_VX, FLUID_VX_PREV)) return e;       // :125-127, in this order
+    if (int e = fl_advect(h, 2, FLUID_VY, FLUID_VY_PREV)) return e;
+    if (int e = fl_advect(h, 3, FLUID_VZ, FLUID_VZ_PREV)) return e;
+    if (int e = fl_project(h)) return e;                                  // :130
+    if (!(h->flags & FLUID_ELIDE_DEAD)) {                                 // :135 (dead work, F2)
+        const int b = 0, f = FLUID_DENS, p = FLUID_BUFFER;
+        if (int e = fl_diffuse(h, 1, &b, &f, &p)) return e;
+    }
+    return fl_advect(h, 0, FLUID_DENS, FLUID_BUFFER);                     // :136
+}
+
+// one iteration of run()'s loop body (simulation.cpp:65-71)
+static inline int fl_run_iteration(fluid_handle* h)
+{
+    if (int e = fl_inflow_density(h)) return e;                           // :65-67
+    if (int e = fl_copy_field(h, FLUID_BUFFER, FLUID_DENS)) return e;     // :70
+    return fl_step_only(h);
+}

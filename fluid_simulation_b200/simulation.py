@@ -1,0 +1,254 @@
+"""Python mirror of the reference's `Simulation` class (simulation.h:11-91) over libfluid_cuda.
+
+Same constructor arguments, same public members and method names (`run`, `step`, `addObstacle`,
+`addDensity`, `setVelocity`); the eleven std::vector<float> fields live in HBM behind a
+`fluid_handle*` and are reached with `get`/`set` in the reference layout, shape (d+2, h+2, w+2).
+The per-phase private methods of the reference are exposed for parity tests (`setBounds`,
+`linearSolver`, `diffuse`, `project`, `advect`) through `fluid_call`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _lib
+
+FIELDS = {
+    "v_x": 0, "v_y": 1, "v_z": 2, "v_x_prev": 3, "v_y_prev": 4, "v_z_prev": 5,
+    "dens": 6, "buffer": 7, "obs": 8, "pressure": 9, "divergence": 10,
+}
+FIELD_NAMES = list(FIELDS)
+
+SOLVER_RB, SOLVER_JACOBI, SOLVER_LEX = 0x0, 0x1, 0x2
+ELIDE_DEAD, NO_TILED = 0x10, 0x20
+
+OP_SET_BOUNDS, OP_LIN_SOLVE, OP_DIFFUSE, OP_DIVERGENCE, OP_GRADIENT = 1, 2, 3, 4, 5
+OP_PROJECT, OP_ADVECT, OP_INFLOW_DENS, OP_INFLOW_VEL, OP_STEP = 6, 7, 8, 9, 10
+
+FRAME_FILES = ("data.bin", "obs.bin", "v_x.bin", "v_y.bin", "v_z.bin")   # simulation.cpp:56-60
+FRAME_FIELDS = ("dens", "obs", "v_x", "v_y", "v_z")                       # simulation.cpp:143-147
+
+
+class FluidError(RuntimeError):
+    pass
+
+
+def _fid(f) -> int:
+    return FIELDS[f] if isinstance(f, str) else int(f)
+
+
+class Simulation:
+    """Drop-in for the reference class; all compute runs in libfluid_cuda on the current GPU."""
+
+    def __init__(self, w, h, d, iter, speed=30, dt=0.05, diff=2.0e-5, visc=1.5e-5, acc=15,
+                 flags=SOLVER_RB, rank=0, nranks=1):
+        self._L = _lib.load()
+        self.width, self.height, self.depth = int(w), int(h), int(d)
+        self.iter, self.speed = int(iter), int(speed)
+        self.dt, self.diff, self.visc = float(dt), float(diff), float(visc)
+        self._acc = int(acc)
+        self.flags = int(flags)
+        self.rank, self.nranks = rank, nranks
+        self.shape = (self.depth + 2, self.height + 2, self.width + 2)
+        self.size = self.shape[0] * self.shape[1] * self.shape[2]             # simulation.cpp:35
+        if nranks == 1:
+            self._h = self._L.fluid_create(w, h, d, speed, dt, diff, visc, acc, flags)
+        else:
+            self._h = self._L.fluid_create_slab(w, h, d, speed, dt, diff, visc, acc, flags, rank, nranks)
+        if not self._h:
+            raise FluidError(self._L.fluid_last_error(None).decode())
+        zlo, dl = C.c_int(), C.c_int()
+        self._L.fluid_get_dims(self._h, None, None, None, C.byref(zlo), C.byref(dl))
+        self.z_lo, self.d_local = zlo.value, dl.value
+        self._frame_bufs = None
+        self._frame_files = None
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def _ck(self, rc):
+        if rc != 0:
+            raise FluidError(f"libfluid_cuda error {rc}: {self._L.fluid_last_error(self._h).decode()}")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            if self._frame_files:
+                self.flush_frames()
+                for f in self._frame_files:
+                    f.close()
+                self._frame_files = None
+            self._L.fluid_destroy(self._h)
+            self._h = None
+        if getattr(self, "_frame_bufs", None):
+            for _, ptr in self._frame_bufs:
+                self._L.fluid_host_free(ptr)
+            self._frame_bufs = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def acc(self):
+        return self._acc
+
+    @acc.setter
+    def acc(self, v):
+        self._acc = int(v)
+        self._ck(self._L.fluid_set_acc(self._h, self._acc))
+
+    # -- field access (replaces direct use of the std::vectors) ------------------------------
+    def set(self, f, arr):
+        a = np.ascontiguousarray(np.asarray(arr, dtype=np.float32).reshape(self.shape))
+        if _fid(f) == FIELDS["obs"]:
+            self._ck(self._L.fluid_upload_obstacles(self._h, a.ctypes.data))
+        else:
+            self._ck(self._L.fluid_upload_field(self._h, _fid(f), a.ctypes.data))
+
+    def get(self, f) -> np.ndarray:
+        out = np.zeros(self.shape, dtype=np.float32)
+        self._ck(self._L.fluid_download_field(self._h, _fid(f), out.ctypes.data))
+        return out
+
+    def state(self) -> dict:
+        return {n: self.get(n) for n in FIELD_NAMES}
+
+    def load_state(self, st: dict):
+        for n, a in st.items():
+            self.set(n, a)
+
+    # -- the reference's public mutators (simulation.cpp:155-178) ----------------------------
+    def addObstacle(self, x, y, z):
+        xyz = np.array([x, y, z], dtype=np.int32)
+        self._ck(self._L.fluid_add_obstacles(self._h, 1, xyz.ctypes.data))
+
+    def addObstacles(self, xyz):
+        xyz = np.ascontiguousarray(np.asarray(xyz, dtype=np.int32).reshape(-1, 3))
+        self._ck(self._L.fluid_add_obstacles(self._h, len(xyz), xyz.ctypes.data))
+
+    def addDensity(self, x, y, z, amount):
+        xyz = np.array([x, y, z], dtype=np.int32)
+        am = np.array([amount], dtype=np.float32)
+        self._ck(self._L.fluid_add_density(self._h, 1, xyz.ctypes.data, am.ctypes.data))
+
+    def setVelocity(self, x, y, z, amount_x, amount_y, amount_z):
+        xyz = np.array([x, y, z], dtype=np.int32)
+        v = np.array([amount_x, amount_y, amount_z], dtype=np.float32)
+        self._ck(self._L.fluid_set_velocity(self._h, 1, xyz.ctypes.data, v.ctypes.data))
+
+    # -- the reference's private phases, for parity tests (simulation.h:33-40) ---------------
+    def _call(self, op, b=0, f=0, prev=0, a=0.0, c=0.0):
+        self._ck(self._L.fluid_call(self._h, op, b, _fid(f), _fid(prev), a, c))
+
+    def setBounds(self, b, f): self._call(OP_SET_BOUNDS, b, f)
+    def linearSolver(self, b, f, prev, a, c): self._call(OP_LIN_SOLVE, b, f, prev, a, c)
+    def diffuse(self, b, f, prev): self._call(OP_DIFFUSE, b, f, prev)
+    def divergence(self): self._call(OP_DIVERGENCE)
+    def gradient(self): self._call(OP_GRADIENT)
+    def project(self): self._call(OP_PROJECT)
+    def advect(self, b, f, prev): self._call(OP_ADVECT, b, f, prev)
+    def inflow_density(self): self._call(OP_INFLOW_DENS)
+    def inflow_velocity(self): self._call(OP_INFLOW_VEL)
+
+    def step(self):
+        """Simulation::step() (simulation.cpp:96-150) without the frame write."""
+        self._call(OP_STEP)
+
+    def run_iterations(self, n=1):
+        """n iterations of run()'s loop body: inlet density, buffer = dens, step() (:65-71)."""
+        self._ck(self._L.fluid_step(self._h, n))
+
+    def sync(self):
+        self._ck(self._L.fluid_sync(self._h))
+
+    # -- statistics (simulation.cpp:73-90) ----------------------------------------------------
+    def stats(self) -> dict:
+        out = (C.c_double * 9)()
+        self._ck(self._L.fluid_stats(self._h, out))
+        keys = ("dens_sum", "dens_min", "dens_max", "vx_min", "vx_max", "vy_min", "vy_max", "vz_min", "vz_max")
+        return dict(zip(keys, list(out)))
+
+    def divergence_norm(self):
+        out = (C.c_double * 2)()
+        self._ck(self._L.fluid_divergence_norm(self._h, out))
+        return out[0], out[1]
+
+    def launch_count(self) -> int:
+        return int(self._L.fluid_launch_count(self._h))
+
+    def timer_start(self):
+        self._ck(self._L.fluid_timer_start(self._h))
+
+    def timer_stop(self) -> float:
+        ms = C.c_float()
+        self._ck(self._L.fluid_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
+    # -- frame dumps (simulation.cpp:56-60, 140-148) ------------------------------------------
+    def _ensure_frame_bufs(self):
+        if self._frame_bufs is None:
+            bufs = []
+            for _ in range(5):
+                ptr = self._L.fluid_host_alloc(self.size * 4)
+                if not ptr:
+                    raise FluidError("pinned host allocation failed")
+                arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float)), shape=(self.size,))
+                bufs.append((arr.reshape(self.shape), ptr))
+            self._frame_bufs = bufs
+        return self._frame_bufs
+
+    def dump_frame_async(self, which=(True, True, True, True, True)):
+        """Start the async D2H of (dens, obs, v_x, v_y, v_z) into pinned buffers; returns the views."""
+        bufs = self._ensure_frame_bufs()
+        ptrs = (C.c_void_p * 5)(*[ptr if w else None for (_, ptr), w in zip(bufs, which)])
+        self._ck(self._L.fluid_dump_frame_async(self._h, ptrs))
+        return [a for a, _ in bufs]
+
+    def frame_wait(self):
+        self._ck(self._L.fluid_frame_wait(self._h))
+
+    def open_frame_files(self, directory="data"):
+        """Open the reference's five output files (simulation.cpp:56-60)."""
+        os.makedirs(directory, exist_ok=True)
+        self._frame_files = [open(os.path.join(directory, n), "wb") for n in FRAME_FILES]
+
+    def flush_frames(self):
+        if self._frame_files and getattr(self, "_frame_pending", False):
+            self.frame_wait()
+            for f, (arr, _) in zip(self._frame_files, self._frame_bufs):
+                f.write(arr.tobytes())
+            self._frame_pending = False
+
+    def run(self, directory="data", dump_every=1, verbose=True):
+        """Simulation::run() (simulation.cpp:49-91): `iter` steps, frames appended to data/*.bin,
+        density sum every 100 steps and the final min/max statistics on stdout."""
+        if verbose:
+            print(f"starting 3-D simulation: {self.width}x{self.height}x{self.depth}  steps = {self.iter}")
+        if directory is not None:
+            self.open_frame_files(directory)
+        self._frame_pending = False
+        for i in range(self.iter):
+            self.run_iterations(1)
+            if directory is not None and (i + 1) % dump_every == 0:
+                self.flush_frames()              # write the previous frame while this step ran
+                self.dump_frame_async()
+                self._frame_pending = True
+            if verbose and (i + 1) % 100 == 0 and i > 0:
+                print(f"step {i + 1}\n  density sum = {self.stats()['dens_sum']:g}")
+        self.flush_frames()
+        st = self.stats()
+        if verbose:
+            print("\n--- statistics -------------------------------------------------")
+            print(f"density  min = {st['dens_min']:g}\ndensity  max = {st['dens_max']:g}")
+            for ax in "xyz":
+                print(f"velocity {ax} min = {st['v' + ax + '_min']:g}\nvelocity {ax} max = {st['v' + ax + '_max']:g}")
+            print("simulation finished")
+        return st

@@ -1,0 +1,145 @@
+/* include/fluid_cuda.h -- C ABI of libfluid_cuda, the B200 (sm_100a) drop-in for the
+ * per-timestep hot path of the reference wind-tunnel solver.
+ *
+ * The reference has no FFI layer: its boundary is the C++ class `Simulation`
+ * (/root/reference/simulation.h:11-91).  A host `Simulation` with the same public
+ * API (fluid_simulation_b200/host/simulation.h) owns a `fluid_handle*` instead of
+ * eleven std::vector<float> and forwards to the entry points below; each entry
+ * point cites the reference code it replaces.
+ *
+ * Conventions
+ *  - plain C types only; every call returns 0 on success or a negative FLUID_E_*
+ *    code and never throws; `fluid_last_error` gives the text.
+ *  - host arrays use the REFERENCE layout: (w+2)*(h+2)*(d+2) floats, index
+ *    x + y*(w+2) + z*(w+2)*(h+2), x fastest (simulation.h:9 `global_at`),
+ *    coordinates 1..dim interior, 0 and dim+1 ghosts.
+ *  - the handle owns all device memory and streams; fields stay resident in HBM.
+ *  - there is NO CPU fallback: every entry point fails with FLUID_E_CUDA when no
+ *    sm_100-class device is usable.
+ *  - one host thread drives a handle; calls are asynchronous on the handle's
+ *    stream unless stated, `fluid_sync` / downloads / stats block.
+ */
+#ifndef FLUID_CUDA_H
+#define FLUID_CUDA_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fluid_handle fluid_handle;
+
+/* field ids = the 11 state vectors of simulation.h:16-27 */
+enum fluid_field {
+    FLUID_VX = 0, FLUID_VY = 1, FLUID_VZ = 2,
+    FLUID_VX_PREV = 3, FLUID_VY_PREV = 4, FLUID_VZ_PREV = 5,
+    FLUID_DENS = 6, FLUID_BUFFER = 7, FLUID_OBS = 8,
+    FLUID_PRESSURE = 9, FLUID_DIVERGENCE = 10, FLUID_NFIELDS = 11
+};
+
+/* creation flags */
+enum fluid_flags {
+    FLUID_SOLVER_RB     = 0x0,  /* default: red-black Gauss-Seidel, colour (i+j+l)&1==0 first        */
+    FLUID_SOLVER_JACOBI = 0x1,  /* Jacobi sweeps                                                      */
+    FLUID_SOLVER_LEX    = 0x2,  /* the reference's lexicographic in-place order (simulation.cpp:260),
+                                   run as a hyperplane wavefront: bit-identical to the 1-thread CPU   */
+    FLUID_SOLVER_MASK   = 0x3,
+    FLUID_ELIDE_DEAD    = 0x10, /* skip diffuse(0,dens,buffer) (simulation.cpp:135): its result is
+                                   fully overwritten by advect (:136); output is bit-identical         */
+    FLUID_NO_TILED      = 0x20  /* force the simple global-memory sweep kernels (debug / A-B checks)  */
+};
+
+/* per-function parity hooks for fluid_call (the reference's private methods, simulation.h:33-40) */
+enum fluid_op {
+    FLUID_OP_SET_BOUNDS = 1,   /* setBounds(b, field)                       simulation.cpp:183 */
+    FLUID_OP_LIN_SOLVE  = 2,   /* linearSolver(b, field, prev, a, c)        simulation.cpp:251 */
+    FLUID_OP_DIFFUSE    = 3,   /* diffuse(b, field, prev)                   simulation.cpp:278 */
+    FLUID_OP_DIVERGENCE = 4,   /* project() part 1: div, p=0, 2x setBounds  simulation.cpp:295-319 */
+    FLUID_OP_GRADIENT   = 5,   /* project() part 3: v -= grad p, 3x bounds  simulation.cpp:322-361 */
+    FLUID_OP_PROJECT    = 6,   /* project(v_x,v_y,v_z,pressure,divergence)  simulation.cpp:289 */
+    FLUID_OP_ADVECT     = 7,   /* advect(b, field, prev)                    simulation.cpp:367 */
+    FLUID_OP_INFLOW_DENS = 8,  /* addDensity(1,j,k,0.001f) on the x=1 face  simulation.cpp:65-67 */
+    FLUID_OP_INFLOW_VEL  = 9,  /* setVelocity(1,j,k,speed,0,0) on x=1 face  simulation.cpp:103-105 */
+    FLUID_OP_STEP        = 10  /* Simulation::step() without run()'s prologue simulation.cpp:96-138 */
+};
+
+enum fluid_error {
+    FLUID_OK = 0, FLUID_E_ARG = -1, FLUID_E_CUDA = -2, FLUID_E_NOMEM = -3,
+    FLUID_E_STATE = -4, FLUID_E_COMM = -5
+};
+
+/* Simulation::Simulation (simulation.cpp:17-44): allocates the 11 zeroed fields in HBM on the
+ * CURRENT CUDA device.  Returns NULL on failure (text via fluid_last_error(NULL)). */
+fluid_handle* fluid_create(int w, int h, int d, int speed, float dt, float diff, float visc,
+                           int acc, unsigned flags);
+
+/* z-slab member of a multi-GPU run: this process owns global planes z_lo..z_lo+d_local-1 of a
+ * w x h x d tunnel.  `rank`/`nranks` order the slabs along z.  Halo planes are
+ * exchanged through the callbacks registered with fluid_set_exchange (NCCL in bench.py). */
+fluid_handle* fluid_create_slab(int w, int h, int d, int speed, float dt, float diff, float visc,
+                                int acc, unsigned flags, int rank, int nranks);
+
+void fluid_destroy(fluid_handle*);
+
+/* parameters that the reference exposes as public data members (simulation.h:44-54) */
+int fluid_set_acc(fluid_handle*, int acc);
+int fluid_get_dims(fluid_handle*, int* w, int* h, int* d, int* z_lo, int* d_local);
+
+/* whole-field transfers in reference layout (replace direct access to the std::vectors).
+ * In slab mode the host array is still the GLOBAL padded volume; each rank moves its planes. */
+int fluid_upload_field(fluid_handle*, int field_id, const float* padded_host);
+int fluid_download_field(fluid_handle*, int field_id, float* padded_host);        /* blocking */
+
+/* addObstacle (simulation.cpp:155) in bulk: the padded obs volume (0.0f / 1.0f), uploaded once;
+ * also builds the per-cell flag volume used by every kernel. */
+int fluid_upload_obstacles(fluid_handle*, const float* obs_padded);
+
+/* sparse mutators, flushed in order before the next device operation:
+ * addObstacle / addDensity / setVelocity (simulation.cpp:155-178), n cells at once. */
+int fluid_add_obstacles(fluid_handle*, int n, const int* xyz /* 3n */);
+int fluid_add_density(fluid_handle*, int n, const int* xyz /* 3n */, const float* amount /* n */);
+int fluid_set_velocity(fluid_handle*, int n, const int* xyz /* 3n */, const float* v /* 3n */);
+
+/* n x { inlet density, buffer = dens, step() } = the body of run()'s loop (simulation.cpp:65-71),
+ * without the frame write.  Asynchronous. */
+int fluid_step(fluid_handle*, int n_steps);
+
+/* one private method of the reference on resident fields (parity hooks). a/c only for LIN_SOLVE. */
+int fluid_call(fluid_handle*, int op, int b, int field_id, int prev_id, float a, float c);
+
+/* frame write of step() (simulation.cpp:140-148): dens, obs, v_x, v_y, v_z in reference layout,
+ * copied on a side stream into `dst[i]` (pinned host memory for overlap; NULL entries skipped).
+ * Ordered after all work submitted so far; returns immediately.  fluid_frame_wait blocks until
+ * the last dump has landed. */
+int fluid_dump_frame_async(fluid_handle*, float* const dst[5]);
+int fluid_frame_wait(fluid_handle*);
+
+/* run()'s statistics (simulation.cpp:73-90) over all padded cells:
+ * out = { sum(dens), min(dens), max(dens), min(v_x), max(v_x), min(v_y), max(v_y), min(v_z), max(v_z) } */
+int fluid_stats(fluid_handle*, double out[9]);
+
+/* sqrt(sum div^2) and max|div| of the stored divergence field over interior fluid cells */
+int fluid_divergence_norm(fluid_handle*, double out[2]);
+
+int fluid_sync(fluid_handle*);
+const char* fluid_last_error(fluid_handle*);
+
+/* pinned host memory helpers for frame buffers (cudaHostAlloc / cudaFreeHost) */
+void* fluid_host_alloc(size_t bytes);
+void  fluid_host_free(void*);
+
+/* device-side timing of the handle's stream (CUDA events): start, stop -> milliseconds */
+int fluid_timer_start(fluid_handle*);
+int fluid_timer_stop(fluid_handle*, float* ms);
+
+/* number of kernels this handle has launched so far (bench.py's gpu_launches) */
+long long fluid_launch_count(fluid_handle*);
+
+/* library/build info: "libfluid_cuda sm_100a ..." */
+const char* fluid_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLUID_CUDA_H */

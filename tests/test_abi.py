@@ -1,0 +1,74 @@
+"""CPU tests of the drop-in boundary: libfluid_cuda.so loads and exports every symbol that
+include/fluid_cuda.h declares; without a GPU the entry points fail loudly (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+from fluid_simulation_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "fluid_cuda.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(fluid_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_header_and_binding_agree():
+    assert header_symbols() == sorted(_lib.SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    for name in header_symbols():
+        assert hasattr(lib, name), name
+    assert b"sm_100a" in lib.fluid_version()
+
+
+def test_library_is_sm100a_only_and_fma_free():
+    out = subprocess.run(["/usr/local/cuda/bin/cuobjdump", "-lelf", _lib.LIB_PATH],
+                         capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    archs = set(re.findall(r"sm_\d+a?", out.stdout))
+    assert archs == {"sm_100a"}, archs
+
+
+def _has_gpu():
+    try:
+        cuda = C.CDLL("libcudart.so")
+    except OSError:
+        return os.path.exists("/dev/nvidia0")
+    n = C.c_int(0)
+    return cuda.cudaGetDeviceCount(C.byref(n)) == 0 and n.value > 0
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidia0"), reason="GPU present")
+def test_no_cpu_fallback_without_gpu():
+    from fluid_simulation_b200 import Simulation, FluidError
+    with pytest.raises(FluidError, match="no CUDA device|no CPU fallback"):
+        Simulation(8, 8, 8, 1)
+
+
+def test_bad_arguments_are_rejected_without_device_work():
+    lib = _lib.load()
+    assert not lib.fluid_create(0, 8, 8, 30, 0.05, 2e-5, 1.5e-5, 15, 0)
+    assert b"bad arguments" in lib.fluid_last_error(None)
+    assert lib.fluid_sync(None) == -1
+    assert lib.fluid_launch_count(None) == 0
+
+
+def test_product_never_touches_the_oracle():
+    """The product path must not import, link or load anything under oracle/."""
+    pkg = os.path.join(ROOT, "fluid_simulation_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".inl", ".cpp", ".h", "Makefile")):
+                txt = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "oracle" not in txt.replace("the CPU oracle", ""), os.path.join(dirpath, f)
+    out = subprocess.run(["ldd", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in out and "fluid_ref" not in out
