@@ -41,8 +41,11 @@ SYMBOLS = {
     "fluid_host_free": (None, [_p]),
     "fluid_timer_start": (_i, [_p]),
     "fluid_timer_stop": (_i, [_p, _fp]),
+    "fluid_profile_enable": (_i, [_p, _i]),
+    "fluid_profile_read": (_i, [_p, _dp]),
     "fluid_launch_count": (C.c_longlong, [_p]),
     "fluid_version": (C.c_char_p, []),
+    "fluid_set_device": (_i, [_i]),
 }
 
 _lib = None

@@ -88,7 +88,6 @@ int fluid_add_obstacles(fluid_handle* h, int n, const int* xyz)
     k_add_obstacles<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_OBS], n, h->d_xyz);
     FL_CHECK_LAUNCH(h);
     h->flags_dirty = true;
-    FL_CUDA(h, cudaStreamSynchronize(h->stream));
     return 0;
 }
 
@@ -100,7 +99,6 @@ int fluid_add_density(fluid_handle* h, int n, const int* xyz, const float* amoun
     if (int e = sparse_stage(h, n, xyz, amount, 1)) return e;
     k_add_density<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_DENS], n, h->d_xyz, h->d_val);
     FL_CHECK_LAUNCH(h);
-    FL_CUDA(h, cudaStreamSynchronize(h->stream));
     return 0;
 }
 
@@ -113,7 +111,6 @@ int fluid_set_velocity(fluid_handle* h, int n, const int* xyz, const float* v)
     k_set_velocity<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY],
                                                           h->field[FLUID_VZ], n, h->d_xyz, h->d_val);
     FL_CHECK_LAUNCH(h);
-    FL_CUDA(h, cudaStreamSynchronize(h->stream));
     return 0;
 }
 

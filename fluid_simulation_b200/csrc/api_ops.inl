@@ -35,8 +35,8 @@ int fluid_call(fluid_handle* h, int op, int b, int field_id, int prev_id, float 
 {
     if (!h) return FLUID_E_ARG;
     const bool needs_field = op == FLUID_OP_SET_BOUNDS || op == FLUID_OP_LIN_SOLVE ||
-                             op == FLUID_OP_DIFFUSE || op == FLUID_OP_ADVECT;
-    const bool needs_prev = op == FLUID_OP_LIN_SOLVE || op == FLUID_OP_DIFFUSE || op == FLUID_OP_ADVECT;
+                             op == FLUID_OP_DIFFUSE || op == FLUID_OP_ADVECT || op == FLUID_OP_COPY;
+    const bool needs_prev = op == FLUID_OP_LIN_SOLVE || op == FLUID_OP_DIFFUSE || op == FLUID_OP_ADVECT || op == FLUID_OP_COPY;
     if (needs_field && (field_id < 0 || field_id >= FLUID_NFIELDS || b < 0 || b > 3))
         return fl_fail(h, FLUID_E_ARG, "fluid_call(op=%d): bad field %d or b %d", op, field_id, b);
     if (needs_prev && (prev_id < 0 || prev_id >= FLUID_NFIELDS || prev_id == field_id))
@@ -52,6 +52,7 @@ int fluid_call(fluid_handle* h, int op, int b, int field_id, int prev_id, float 
         case FLUID_OP_INFLOW_DENS: return fl_inflow_density(h);
         case FLUID_OP_INFLOW_VEL:  return fl_inflow_velocity(h);
         case FLUID_OP_STEP:        return fl_step_only(h);
+        case FLUID_OP_COPY:        return fl_copy_field(h, field_id, prev_id);
     }
     return fl_fail(h, FLUID_E_ARG, "fluid_call: unknown op %d", op);
 }

@@ -134,6 +134,8 @@ void fluid_destroy(fluid_handle* h)
     for (int i = 0; i < 5; ++i) cudaFree(h->frame_staging[i]);
     cudaFree(h->cflags); cudaFree(h->staging); cudaFree(h->d_partial); cudaFree(h->d_out);
     cudaFree(h->d_xyz); cudaFree(h->d_val);
+    for (auto& r : h->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    for (auto e : h->ev_pool) cudaEventDestroy(e);
     if (h->ev_frame_packed) cudaEventDestroy(h->ev_frame_packed);
     if (h->ev_frame_done) cudaEventDestroy(h->ev_frame_done);
     if (h->ev_a) cudaEventDestroy(h->ev_a);
@@ -172,6 +174,13 @@ int fluid_sync(fluid_handle* h)
 
 long long fluid_launch_count(fluid_handle* h) { return h ? h->launches : 0; }
 
+int fluid_set_device(int device)
+{
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fl_fail(nullptr, FLUID_E_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    return 0;
+}
+
 void* fluid_host_alloc(size_t bytes)
 {
     void* p = nullptr;
@@ -192,6 +201,30 @@ int fluid_timer_stop(fluid_handle* h, float* ms)
     FL_CUDA(h, cudaEventRecord(h->ev_t1, h->stream));
     FL_CUDA(h, cudaEventSynchronize(h->ev_t1));
     FL_CUDA(h, cudaEventElapsedTime(ms, h->ev_t0, h->ev_t1));
+    return 0;
+}
+
+// per-solve device timing: every linearSolver call is bracketed by a CUDA event pair on the
+// handle's stream while enabled; fluid_profile_read syncs, sums and resets.
+int fluid_profile_enable(fluid_handle* h, int on)
+{
+    if (!h) return FLUID_E_ARG;
+    h->profiling = on != 0;
+    return 0;
+}
+int fluid_profile_read(fluid_handle* h, double out[3])
+{
+    if (!h || !out) return FLUID_E_ARG;
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    double ms = 0.0, sweeps = 0.0;
+    for (auto& r : h->prof) {
+        float t = 0.0f;
+        FL_CUDA(h, cudaEventElapsedTime(&t, r.a, r.b));
+        ms += t; sweeps += (double)r.field_sweeps;
+        h->ev_pool.push_back(r.a); h->ev_pool.push_back(r.b);
+    }
+    out[0] = ms; out[1] = sweeps; out[2] = (double)h->prof.size();
+    h->prof.clear();
     return 0;
 }
 

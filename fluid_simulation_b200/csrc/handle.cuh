@@ -28,7 +28,11 @@ struct fluid_handle {
     std::string err;
     // multi-GPU halo exchange hook (slab mode); see fluid_cuda.cu
     void* comm = nullptr;
-    // wavefront (LEX) scratch
+    // optional per-solve CUDA-event timing (fluid_profile_*): one event pair per linearSolver call
+    bool profiling = false;
+    struct ProfRec { cudaEvent_t a, b; long long field_sweeps; };
+    std::vector<ProfRec> prof;
+    std::vector<cudaEvent_t> ev_pool;
     int sm_count = 148;
 };
 

@@ -104,6 +104,26 @@ __global__ void __launch_bounds__(256) k_set_bounds(Grid g, float* __restrict__ 
     fl_store_bounded(g, field, flags, b, p.x0, p.y, p.zl, raw);
 }
 
+// ---- edge / corner ghosts --------------------------------------------------------------------
+// setBounds never writes cells with two or more ghost coordinates (simulation.cpp:187-215), so an
+// in-place solver keeps whatever they held.  Ping-pong (Jacobi) partners get them copied once per
+// solve so the result is independent of which buffer the last sweep landed in.
+__global__ void k_copy_edges(Grid g, const float* __restrict__ src, float* __restrict__ dst)
+{
+    const int per = 2 * (g.W + 2) + 2 * g.H;                 // perimeter cells of one plane
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int zl = blockIdx.y;
+    if (t >= per) return;
+    int x, y;
+    if (t < g.W + 2)            { x = t; y = 0; }
+    else if (t < 2 * (g.W + 2)) { x = t - (g.W + 2); y = g.H + 1; }
+    else if (t < 2 * (g.W + 2) + g.H) { x = 0; y = 1 + t - 2 * (g.W + 2); }
+    else                        { x = g.W + 1; y = 1 + t - 2 * (g.W + 2) - g.H; }
+    const int gz = g.zlo + zl - 1;
+    const int nghost = (x == 0 || x == g.W + 1) + (y == 0 || y == g.H + 1) + (gz == 0 || gz == g.D + 1);
+    if (nghost >= 2) { long long c = fl_idx(g, x, y, zl); dst[c] = src[c]; }
+}
+
 // ---- sparse mutators (addObstacle / addDensity / setVelocity, simulation.cpp:155-178) --------
 // xyz are GLOBAL 0..dim+1 coordinates; cells outside this slab's planes (incl. halos) are skipped.
 __global__ void k_add_density(Grid g, float* __restrict__ dens, int n, const int* __restrict__ xyz,

@@ -50,8 +50,31 @@ static inline int fl_set_bounds(fluid_handle* h, int b, int fid)
 
 // linearSolver(b, field, prev, a, c) for up to three fields that share a and c
 // (simulation.cpp:251-273): acc sweeps, setBounds after each.
+static inline cudaEvent_t fl_prof_event(fluid_handle* h)
+{
+    cudaEvent_t e = nullptr;
+    if (!h->ev_pool.empty()) { e = h->ev_pool.back(); h->ev_pool.pop_back(); }
+    else cudaEventCreate(&e);
+    return e;
+}
+
+static inline int fl_lin_solve_impl(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
+                                    float a, float c);
+
 static inline int fl_lin_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
                                float a, float c)
+{
+    if (!h->profiling) return fl_lin_solve_impl(h, nb, b, fid, pid, a, c);
+    fluid_handle::ProfRec r{ fl_prof_event(h), fl_prof_event(h), (long long)nb * h->acc };
+    cudaEventRecord(r.a, h->stream);
+    int e = fl_lin_solve_impl(h, nb, b, fid, pid, a, c);
+    cudaEventRecord(r.b, h->stream);
+    h->prof.push_back(r);
+    return e;
+}
+
+static inline int fl_lin_solve_impl(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
+                                    float a, float c)
 {
     if (int e = fl_rebuild_flags(h)) return e;
     if (h->acc <= 0) return 0;
@@ -70,6 +93,13 @@ static inline int fl_lin_solve(fluid_handle* h, int nb, const int* b, const int*
     for (int i = 0; i < nb; ++i) {
         cur[i] = h->field[fid[i]]; alt[i] = h->scratch[i];
         sb.rhs[i] = h->field[pid[i]]; sb.b[i] = b[i];
+    }
+    if (solver == FLUID_SOLVER_JACOBI) {
+        dim3 ge((2 * (g.W + 2) + 2 * g.H + 127) / 128, g.Dl + 2);
+        for (int i = 0; i < nb; ++i) {
+            k_copy_edges<<<ge, 128, 0, h->stream>>>(g, cur[i], alt[i]);
+            FL_CHECK_LAUNCH(h);
+        }
     }
     for (int k = 0; k < h->acc; ++k) {                                    // simulation.cpp:258
         if (solver == FLUID_SOLVER_JACOBI) {

@@ -25,7 +25,7 @@ SOLVER_RB, SOLVER_JACOBI, SOLVER_LEX = 0x0, 0x1, 0x2
 ELIDE_DEAD, NO_TILED = 0x10, 0x20
 
 OP_SET_BOUNDS, OP_LIN_SOLVE, OP_DIFFUSE, OP_DIVERGENCE, OP_GRADIENT = 1, 2, 3, 4, 5
-OP_PROJECT, OP_ADVECT, OP_INFLOW_DENS, OP_INFLOW_VEL, OP_STEP = 6, 7, 8, 9, 10
+OP_PROJECT, OP_ADVECT, OP_INFLOW_DENS, OP_INFLOW_VEL, OP_STEP, OP_COPY = 6, 7, 8, 9, 10, 11
 
 FRAME_FILES = ("data.bin", "obs.bin", "v_x.bin", "v_y.bin", "v_z.bin")   # simulation.cpp:56-60
 FRAME_FIELDS = ("dens", "obs", "v_x", "v_y", "v_z")                       # simulation.cpp:143-147
@@ -144,6 +144,24 @@ class Simulation:
         v = np.array([amount_x, amount_y, amount_z], dtype=np.float32)
         self._ck(self._L.fluid_set_velocity(self._h, 1, xyz.ctypes.data, v.ctypes.data))
 
+    def pinned_array(self, shape, dtype):
+        """numpy view of a pinned host allocation (freed with the Simulation)."""
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        ptr = self._L.fluid_host_alloc(max(n, 1))
+        if not ptr:
+            raise FluidError("pinned host allocation failed")
+        self._pinned = getattr(self, "_pinned", [])
+        self._pinned.append(ptr)
+        buf = (C.c_char * max(n, 1)).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def add_density_cells(self, xyz, amount):
+        """addDensity for n cells at once; xyz int32 (n,3), amount float32 (n,) (host arrays)."""
+        self._ck(self._L.fluid_add_density(self._h, len(xyz), xyz.ctypes.data, amount.ctypes.data))
+
+    def set_velocity_cells(self, xyz, v):
+        self._ck(self._L.fluid_set_velocity(self._h, len(xyz), xyz.ctypes.data, v.ctypes.data))
+
     # -- the reference's private phases, for parity tests (simulation.h:33-40) ---------------
     def _call(self, op, b=0, f=0, prev=0, a=0.0, c=0.0):
         self._ck(self._L.fluid_call(self._h, op, b, _fid(f), _fid(prev), a, c))
@@ -183,6 +201,15 @@ class Simulation:
 
     def launch_count(self) -> int:
         return int(self._L.fluid_launch_count(self._h))
+
+    def profile(self, on=True):
+        self._ck(self._L.fluid_profile_enable(self._h, int(on)))
+
+    def profile_read(self):
+        """(ms inside linearSolver, field-sweeps, solver calls) since the last read."""
+        out = (C.c_double * 3)()
+        self._ck(self._L.fluid_profile_read(self._h, out))
+        return out[0], out[1], out[2]
 
     def timer_start(self):
         self._ck(self._L.fluid_timer_start(self._h))

@@ -61,7 +61,8 @@ enum fluid_op {
     FLUID_OP_ADVECT     = 7,   /* advect(b, field, prev)                    simulation.cpp:367 */
     FLUID_OP_INFLOW_DENS = 8,  /* addDensity(1,j,k,0.001f) on the x=1 face  simulation.cpp:65-67 */
     FLUID_OP_INFLOW_VEL  = 9,  /* setVelocity(1,j,k,speed,0,0) on x=1 face  simulation.cpp:103-105 */
-    FLUID_OP_STEP        = 10  /* Simulation::step() without run()'s prologue simulation.cpp:96-138 */
+    FLUID_OP_STEP        = 10, /* Simulation::step() without run()'s prologue simulation.cpp:96-138 */
+    FLUID_OP_COPY        = 11  /* field = prev (buffer = dens, v_prev = v)    simulation.cpp:70, 108-110 */
 };
 
 enum fluid_error {
@@ -133,11 +134,21 @@ void  fluid_host_free(void*);
 int fluid_timer_start(fluid_handle*);
 int fluid_timer_stop(fluid_handle*, float* ms);
 
+/* per-solve device timing for bench.py's roofline: while enabled every linearSolver call
+ * (simulation.cpp:251) is bracketed by CUDA events on the handle's stream.  read() blocks and
+ * returns { total ms inside linearSolver, field-sweeps executed (fields x acc), solver calls }
+ * since the last read, then resets. */
+int fluid_profile_enable(fluid_handle*, int on);
+int fluid_profile_read(fluid_handle*, double out[3]);
+
 /* number of kernels this handle has launched so far (bench.py's gpu_launches) */
 long long fluid_launch_count(fluid_handle*);
 
 /* library/build info: "libfluid_cuda sm_100a ..." */
 const char* fluid_version(void);
+
+/* select the CUDA device subsequent fluid_create calls of this thread use (cudaSetDevice) */
+int fluid_set_device(int device);
 
 #ifdef __cplusplus
 }
