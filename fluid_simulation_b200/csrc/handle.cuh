@@ -28,6 +28,7 @@ struct fluid_handle {
     std::string err;
     // multi-GPU halo exchange hook (slab mode); see fluid_cuda.cu
     void* comm = nullptr;
+    void* tiled = nullptr;           // TiledState (tensor maps), tiled.cuh
     // optional per-solve CUDA-event timing (fluid_profile_*): one event pair per linearSolver call
     bool profiling = false;
     struct ProfRec { cudaEvent_t a, b; long long field_sweeps; };

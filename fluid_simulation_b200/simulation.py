@@ -22,7 +22,7 @@ FIELDS = {
 FIELD_NAMES = list(FIELDS)
 
 SOLVER_RB, SOLVER_JACOBI, SOLVER_LEX = 0x0, 0x1, 0x2
-ELIDE_DEAD, NO_TILED = 0x10, 0x20
+ELIDE_DEAD, NO_TILED, TILED_ALWAYS = 0x10, 0x20, 0x40
 
 OP_SET_BOUNDS, OP_LIN_SOLVE, OP_DIFFUSE, OP_DIVERGENCE, OP_GRADIENT = 1, 2, 3, 4, 5
 OP_PROJECT, OP_ADVECT, OP_INFLOW_DENS, OP_INFLOW_VEL, OP_STEP, OP_COPY = 6, 7, 8, 9, 10, 11

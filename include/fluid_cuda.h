@@ -47,7 +47,8 @@ enum fluid_flags {
     FLUID_SOLVER_MASK   = 0x3,
     FLUID_ELIDE_DEAD    = 0x10, /* skip diffuse(0,dens,buffer) (simulation.cpp:135): its result is
                                    fully overwritten by advect (:136); output is bit-identical         */
-    FLUID_NO_TILED      = 0x20  /* force the simple global-memory sweep kernels (debug / A-B checks)  */
+    FLUID_NO_TILED      = 0x20, /* force the simple global-memory sweep kernels (debug / A-B checks)  */
+    FLUID_TILED_ALWAYS  = 0x40  /* use the TMA/shared-memory sweep kernel even on tiny grids (tests)  */
 };
 
 /* per-function parity hooks for fluid_call (the reference's private methods, simulation.h:33-40) */
