@@ -3,7 +3,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -lineinfo (csrc/Makefile).
 // There is no CPU path: without a usable CUDA device every entry point fails.
 #include "solver.cuh"
-#include "tiled.cuh"
+#include "sweep_stream.cuh"
 #include "wavefront.cuh"
 #include <cstring>
 #include <new>

@@ -1,0 +1,21 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, bench line, ncu launch list + full capture of the sweep kernel.
+# Usage (from the repo root on the box): bash scripts/gpu_check.sh [tag]
+TAG=${1:-r1}
+OUT=gpurun_out/$TAG
+mkdir -p $OUT
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/smi.txt 2>&1
+python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/pytest_gpu.log
+tail -3 $OUT/pytest_gpu.log
+python bench.py --steps 5 --warmup 3 > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?"
+cat $OUT/bench.json
+BENCH="python bench.py --steps 1 --warmup 3 --no-cpu"
+$BENCH > $OUT/plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -s 1500 -c 700 --csv \
+    --log-file $OUT/launches.csv $BENCH > $OUT/ncu_launches.log 2>&1
+echo "ncu launches rc=$?"
+$BENCH > $OUT/plain2.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:k_sweep_tiled -s 600 -c 3 \
+    -o $OUT/prof_sweep $BENCH > $OUT/ncu_full.log 2>&1
+echo "ncu full rc=$?"
+ls -la $OUT

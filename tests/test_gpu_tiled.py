@@ -1,6 +1,7 @@
-"""The TMA/shared-memory tiled sweep kernel (csrc/tiled.cuh) against the ordering-matched CPU
-oracle, bit-exact, over tile-boundary, ragged and multi-chunk shapes; and against the simple
-global-memory kernels (FLUID_NO_TILED) on a larger grid."""
+"""The TMA-fed register-streaming sweep kernel (csrc/sweep_stream.cuh) against the ordering-matched
+CPU oracle, bit-exact, over warp-column, row-tile, ragged and multi-chunk shapes; and against the
+simple global-memory kernels (FLUID_NO_TILED) on a larger grid.  Shapes with W % 4 != 0 or W > 512
+exercise the documented hand-over to the simple kernels under FLUID_TILED_ALWAYS."""
 import os
 
 import numpy as np
@@ -13,9 +14,11 @@ pytestmark = pytest.mark.gpu
 
 TILED_ALWAYS, NO_TILED = 0x40, 0x20
 SOLVERS = [("rb", 0x0, ORDER_RB), ("jacobi", 0x1, ORDER_JACOBI)]
-# W around the 128-cell tile width, H around the 30-row tile height, D around chunk sizes
+# W around the 128-cell warp columns (1, 2, 4 columns), H around the row-tile heights (30 / 16 / 6
+# owned rows), D around chunk sizes
 SHAPES = [(130, 33, 9), (128, 30, 8), (127, 31, 17), (257, 61, 12), (100, 29, 5), (24, 16, 12),
-          (5, 3, 2), (1, 1, 1), (260, 8, 4), (129, 90, 3)]
+          (5, 3, 2), (1, 1, 1), (260, 8, 4), (129, 90, 3), (256, 40, 20), (512, 13, 9), (384, 20, 7),
+          (64, 64, 33), (132, 70, 6), (8, 2, 2), (4, 1, 1), (252, 17, 5), (516, 6, 3)]
 
 
 def pair(w, h, d, acc, flag, order, seed=7):
