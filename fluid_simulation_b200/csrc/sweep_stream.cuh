@@ -31,13 +31,13 @@
 #include <map>
 #include <cstdlib>
 
-#define SW_BOXW   136                    // floats per box row: halo quad + 32 quads + halo quad
-#define SW_AHEAD  3                      // TMA prefetch distance in planes
-#define SW_NSLOT  (SW_AHEAD + 2)
+#define SW_BOXW   136                    // floats per x box row: halo quad + 32 quads + halo quad
+#define SW_RBOXW  128                    // floats per rhs box row (no halo columns)
+#define SW_SMEM_MAX 232448               // 227 KB of dynamic shared memory per CTA on sm_100
 
 struct alignas(64) StreamArgs {
     CUtensorMap map[3];                  // source field of each batched solve (box SW_BOXW x BR x 1)
-    const float* rhs[3];
+    CUtensorMap rmap[3];                 // its right-hand side (box SW_RBOXW x BR-2 x 1)
     float* dst[3];
     int b[3];
     const unsigned char* flags;
@@ -80,7 +80,29 @@ __device__ __forceinline__ void sw_fence_proxy_async()
 {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
-__device__ __forceinline__ float4 sw_lds4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+// 128-bit shared load the compiler cannot split: when only two lanes of the quad are live it would
+// otherwise emit two scalar LDS, each a 4-way bank conflict across the warp (stride 16 B).
+__device__ __forceinline__ float4 sw_lds4(const float* p)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(sw_smem(p)));
+    return v;
+}
+// cell left of a quad (L) / right of it (R): the neighbour lane's outer cell by shuffle; the two
+// edge lanes of the warp read the halo column of the shared-memory box instead.
+__device__ __forceinline__ float sw_left(const float4& c, const float* row_quad, int lane)
+{
+    float L = __shfl_up_sync(0xffffffffu, c.w, 1);
+    if (lane == 0) L = row_quad[-1];
+    return L;
+}
+__device__ __forceinline__ float sw_right(const float4& c, const float* row_quad, int lane)
+{
+    float R = __shfl_down_sync(0xffffffffu, c.x, 1);
+    if (lane == 31) R = row_quad[4];
+    return R;
+}
 __device__ __forceinline__ void   sw_sts4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
 // relax the two lanes (E, E+2) of quad c in place.  L / R are the cells left of lane 0 / right of
@@ -140,24 +162,157 @@ __device__ __forceinline__ void sw_store(const Grid& g, float* __restrict__ out,
 
 template <int TXW, int NP>
 struct SwGeom {
-    static constexpr int BR = 2 * NP + 2;                            // box rows: TY owned + 2 halo + 2 read-only
+    static constexpr int BR = 2 * NP + 2;                            // x box rows: TY owned + 2 halo + 2 read-only
     static constexpr int TY = 2 * NP - 2;                            // owned rows per CTA
-    static constexpr int BOXF = (SW_BOXW * BR + 31) / 32 * 32;       // floats per box, 128-byte multiple
-    static constexpr int SLOTF = TXW * BOXF;                         // one plane of the CTA
+    static constexpr int BOXF = (SW_BOXW * BR + 31) / 32 * 32;       // floats per x box, 128-byte multiple
+    static constexpr int RBOXF = SW_RBOXW * (BR - 2);                // floats per rhs box (owned + halo rows)
+    static constexpr int XSLOTF = TXW * BOXF;                        // the x boxes of one plane
+    static constexpr int SLOTF = TXW * (BOXF + RBOXF);               // one plane of the CTA: x boxes, then rhs boxes
     static constexpr int THREADS = 32 * TXW * NP;
-    static constexpr size_t SMEM = (size_t)(SW_NSLOT + 2) * SLOTF * sizeof(float);
+    static constexpr int TX_BYTES = TXW * (SW_BOXW * BR + SW_RBOXW * (BR - 2)) * 4;
+    // ring depth: as many planes in flight as shared memory allows (the TMA ring IS the latency hiding:
+    // one CTA per SM, so the bytes in flight are the bytes of the slots being filled)
+    static constexpr int NSLOT_FIT = (SW_SMEM_MAX - 2 * XSLOTF * 4 - 1024) / (SLOTF * 4);
+    static constexpr int NSLOT = NSLOT_FIT > 8 ? 8 : NSLOT_FIT;
+    static constexpr int AHEAD = NSLOT - 2;                          // TMA prefetch distance in planes
+    static constexpr size_t SMEM = (size_t)(NSLOT * SLOTF + 2 * XSLOTF) * sizeof(float);
+    static_assert(NSLOT >= 3, "tile too large for the shared-memory ring");
 };
+
+// Per-thread state of the streaming sweep: the register-resident z-column of the two rows and
+// everything that is constant along z.  The column is a ring of four planes: in unrolled step U
+// Q[U] is plane p-2 (two behind), Q[U+1] plane p-1, Q[U+2] plane p and Q[U+3] receives plane p+1,
+// so advancing by one plane renames registers instead of moving them.  R (rhs, read from the TMA
+// slot of plane p) and F (flag bytes, fetched from global memory three planes ahead of their use)
+// follow the same indexing.
+struct SwThread {
+    float4 QA[4], QB[4], RA[4], RB[4];
+    unsigned FA[4], FB[4];
+    unsigned oA, oB;                       // element offsets of the two quads in plane p+1
+    int offA, offB;                        // shared-memory offsets of the two x quads inside a slot
+    int roffA, roffB;                      // ... and of the two rhs quads
+    int lane;
+    unsigned eA, eB;                       // x / y edge bits
+    unsigned sink;                         // keeps the dead lanes of 128-bit shared loads alive (see sw_lds4)
+    bool intA, intB, ownA, ownB, pub_gl, pub_gr, pub_nl, pub_nr;
+};
+
+// 128-bit shared load of a row neighbour of which only lanes (E, E+2) are consumed.  ptxas would
+// narrow it to two scalar LDS -- each a 4-way bank conflict across the warp (lane stride 16 B), 8
+// wavefronts instead of 4 -- so the two dead lanes are folded into a sink word (one LOP3).
+template <int E>
+__device__ __forceinline__ float4 sw_lds4_half(const float* p, unsigned& sink)
+{
+    const float4 v = sw_lds4(p);
+    if (E == 0) sink |= __float_as_uint(v.y) | __float_as_uint(v.w);
+    else        sink |= __float_as_uint(v.x) | __float_as_uint(v.z);
+    return v;
+}
+
+// one plane of the pipeline: stage 0 on plane p, stage 1 on plane p-1 (Jacobi: the whole update of
+// plane p).  U = position in the 4-step unrolled loop, E = (z_global(p) + 1) & 1, both static.
+template <int BOXF, int XSLOTF, int MODE, int U, int E>
+__device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float* __restrict__ out, int b,
+                                        unsigned zmask4, int p, int za, int zb, int p_last,
+                                        const float* Up, const float* Un, unsigned long long* bar_n,
+                                        unsigned phase_n, float* vbuf)
+{
+    const Grid& g = A.g;
+    const float a = A.a, cr = A.c_recip;
+    const unsigned plane = (unsigned)g.plane;
+    constexpr int I2 = U & 3, IM = (U + 1) & 3, IC = (U + 2) & 3, IN = (U + 3) & 3;
+    const int offA = t.offA, offB = t.offB;
+    // flag bytes of plane p+2 (t.oA addresses plane p+1): consumed by the store of that plane, which
+    // is three steps away for red-black and two for Jacobi
+    if (p + 2 <= zb) {
+        t.FA[I2] = *reinterpret_cast<const unsigned*>(A.flags + t.oA + plane);
+        t.FB[I2] = *reinterpret_cast<const unsigned*>(A.flags + t.oB + plane);
+    }
+    // rhs of plane p sits in the slot of plane p (arrived at least one step ago)
+    t.RA[IC] = sw_lds4(Up + t.roffA); t.RB[IC] = sw_lds4(Up + t.roffB);
+    if (p + 1 <= p_last) {
+        sw_mbar_wait(bar_n, phase_n);
+        t.QA[IN] = sw_lds4(Un + offA); t.QB[IN] = sw_lds4(Un + offB);
+    }
+    float4& cA = t.QA[IC]; float4& cB = t.QB[IC];
+    const float4& mA = t.QA[IM]; const float4& mB = t.QB[IM];
+
+    if (MODE == 0) {
+        // ---- Jacobi: relax all four lanes of plane p from the old planes p-1, p, p+1 --------------
+        if (p >= za && p <= zb) {
+            const float4 ymA = sw_lds4(Up + offA - SW_BOXW), ypB = sw_lds4(Up + offB + SW_BOXW);
+            const float LA = sw_left(cA, Up + offA, t.lane), RA = sw_right(cA, Up + offA, t.lane);
+            const float LB = sw_left(cB, Up + offB, t.lane), RB = sw_right(cB, Up + offB, t.lane);
+            const unsigned zbits = (g.zlo + p - 1 == 1 ? SW_ZLO : 0u) | (g.zlo + p - 1 == g.D ? SW_ZHI : 0u);
+            float4 e = cA, f = cA;
+            sw_relax2<0>(e, LA, RA, cB, ymA, t.QA[IN], mA, t.RA[IC], a, cr);
+            sw_relax2<1>(f, LA, RA, cB, ymA, t.QA[IN], mA, t.RA[IC], a, cr);
+            if (t.ownA) sw_store(g, out, t.oA - plane, make_float4(e.x, f.y, e.z, f.w), t.FA[IC], b, zmask4, t.eA | zbits);
+            e = cB; f = cB;
+            sw_relax2<0>(e, LB, RB, ypB, cA, t.QB[IN], mB, t.RB[IC], a, cr);
+            sw_relax2<1>(f, LB, RB, ypB, cA, t.QB[IN], mB, t.RB[IC], a, cr);
+            if (t.ownB) sw_store(g, out, t.oB - plane, make_float4(e.x, f.y, e.z, f.w), t.FB[IC], b, zmask4, t.eB | zbits);
+        }
+    } else {
+        // ---- stage 0: colour-0 cells of plane p, in registers --------------------------------------
+        if (p >= 1 && p <= g.Dl) {
+            const float4 ymA = sw_lds4_half<E>(Up + offA - SW_BOXW, t.sink);
+            const float4 ypB = sw_lds4_half<1 - E>(Up + offB + SW_BOXW, t.sink);
+            float4 tA = cA, tB = cB;
+            if (E == 0) {
+                const float L = sw_left(cA, Up + offA, t.lane), R = sw_right(cB, Up + offB, t.lane);
+                sw_relax2<0>(tA, L, 0.0f, cB, ymA, t.QA[IN], mA, t.RA[IC], a, cr);
+                sw_relax2<1>(tB, 0.0f, R, ypB, cA, t.QB[IN], mB, t.RB[IC], a, cr);
+            } else {
+                const float R = sw_right(cA, Up + offA, t.lane), L = sw_left(cB, Up + offB, t.lane);
+                sw_relax2<1>(tA, 0.0f, R, cB, ymA, t.QA[IN], mA, t.RA[IC], a, cr);
+                sw_relax2<0>(tB, L, 0.0f, ypB, cA, t.QB[IN], mB, t.RB[IC], a, cr);
+            }
+            if (t.intA) cA = tA;
+            if (t.intB) cB = tB;
+        }
+        // publish plane p (colour 0 new, colour 1 old) for the row / warp neighbours
+        float* Vp = vbuf + (U & 1) * XSLOTF;
+        sw_sts4(Vp + offA, cA); sw_sts4(Vp + offB, cB);
+        if (t.pub_nl) { Vp[offA + 128 - BOXF] = cA.x; Vp[offB + 128 - BOXF] = cB.x; }
+        if (t.pub_nr) { Vp[offA + BOXF - 125] = cA.w; Vp[offB + BOXF - 125] = cB.w; }
+        if (t.pub_gl) { Vp[offA - 1] = Up[offA - 1]; Vp[offB - 1] = Up[offB - 1]; }           // x = 0 ghosts
+        if (t.pub_gr) { Vp[offA + 4] = Up[offA + 4]; Vp[offB + 4] = Up[offB + 4]; }           // x = W+1 ghosts
+        // ---- stage 1: colour-1 cells of plane p-1 from colour-0 values, then setBounds -------------
+        const int q = p - 1;
+        if (q >= za && q <= zb) {
+            const float* Vq = vbuf + ((U + 1) & 1) * XSLOTF;         // published (and synced) last iteration
+            const float4 ymA = sw_lds4_half<E>(Vq + offA - SW_BOXW, t.sink);
+            const float4 ypB = sw_lds4_half<1 - E>(Vq + offB + SW_BOXW, t.sink);
+            float4 tA = mA, tB = mB;
+            if (E == 0) {
+                const float L = sw_left(mA, Vq + offA, t.lane), R = sw_right(mB, Vq + offB, t.lane);
+                sw_relax2<0>(tA, L, 0.0f, mB, ymA, cA, t.QA[I2], t.RA[IM], a, cr);
+                sw_relax2<1>(tB, 0.0f, R, ypB, mA, cB, t.QB[I2], t.RB[IM], a, cr);
+            } else {
+                const float R = sw_right(mA, Vq + offA, t.lane), L = sw_left(mB, Vq + offB, t.lane);
+                sw_relax2<1>(tA, 0.0f, R, mB, ymA, cA, t.QA[I2], t.RA[IM], a, cr);
+                sw_relax2<0>(tB, L, 0.0f, ypB, mA, cB, t.QB[I2], t.RB[IM], a, cr);
+            }
+            const int gzq = g.zlo + q - 1;
+            const unsigned zbits = (gzq == 1 ? SW_ZLO : 0u) | (gzq == g.D ? SW_ZHI : 0u);
+            if (t.ownA) sw_store(g, out, t.oA - 2 * plane, tA, t.FA[IM], b, zmask4, t.eA | zbits);
+            if (t.ownB) sw_store(g, out, t.oB - 2 * plane, tB, t.FB[IM], b, zmask4, t.eB | zbits);
+        }
+    }
+}
 
 // MODE 0 = Jacobi, 1 = red-black (colour 0 = (x+y+z) even first)
 template <int TXW, int NP, int MODE>
 __global__ void __launch_bounds__(32 * TXW * NP, 1) k_sweep_stream(const __grid_constant__ StreamArgs A)
 {
     using GE = SwGeom<TXW, NP>;
-    constexpr int BOXF = GE::BOXF, SLOTF = GE::SLOTF;
+    constexpr int BOXF = GE::BOXF, RBOXF = GE::RBOXF, SLOTF = GE::SLOTF, XSLOTF = GE::XSLOTF;
+    constexpr int NSLOT = GE::NSLOT, AHEAD = GE::AHEAD;
     extern __shared__ __align__(128) float sw_mem[];
-    __shared__ unsigned long long bars[SW_NSLOT];
-    float* const uring = sw_mem;                                     // SW_NSLOT TMA slots (source field)
-    float* const vbuf = sw_mem + SW_NSLOT * SLOTF;                   // 2 slots: plane after stage 0
+    __shared__ unsigned long long bars[NSLOT];
+    float* const uring = sw_mem;                                     // NSLOT TMA slots (x boxes + rhs boxes)
+    float* const vbuf = sw_mem + NSLOT * SLOTF;                      // 2 slots: plane after stage 0
 
     const Grid& g = A.g;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -168,167 +323,91 @@ __global__ void __launch_bounds__(32 * TXW * NP, 1) k_sweep_stream(const __grid_
     const int zb = min(za + A.zc - 1, g.Dl);
     const int pa = za - 1, pb = zb + 1;                              // stage-0 plane range
     const int p_first = max(pa - 1, 0), p_last = min(pb + 1, g.Dl + 1);
-    const float a = A.a, cr = A.c_recip;
     const int b = A.b[batch];
     const unsigned zmask4 = fl_zero_mask(b) * 0x01010101u;
-    const float* __restrict__ rhs = A.rhs[batch];
-    const unsigned char* __restrict__ flags = A.flags;
     float* __restrict__ out = A.dst[batch];
 
-    auto slot_of = [&](int p) { return (p - p_first) % SW_NSLOT; };
-    auto uslot = [&](int p) -> float* { return uring + slot_of(p) * SLOTF; };
-    auto wait_plane = [&](int p) { sw_mbar_wait(&bars[slot_of(p)], ((p - p_first) / SW_NSLOT) & 1); };
-    auto issue = [&](int p) {
-        const int s = slot_of(p);
-        sw_mbar_expect_tx(&bars[s], TXW * SW_BOXW * GE::BR * 4);
+    auto issue = [&](int p, int s) {                                 // plane p -> ring slot s
+        sw_mbar_expect_tx(&bars[s], GE::TX_BYTES);
+        float* slot = uring + s * SLOTF;
 #pragma unroll
-        for (int i = 0; i < TXW; ++i)
-            sw_tma_load_3d(uring + s * SLOTF + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p, &bars[s]);
+        for (int i = 0; i < TXW; ++i) {
+            sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p, &bars[s]);
+            sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p, &bars[s]);
+        }
     };
 
     if (tid == 0) {
-        for (int i = 0; i < SW_NSLOT; ++i) sw_mbar_init(&bars[i], 1);
+        for (int i = 0; i < NSLOT; ++i) sw_mbar_init(&bars[i], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    // ring slot of plane p is (p - p_first) mod NSLOT; the first NSLOT planes go out at once
     if (tid == 0)
-        for (int p = p_first; p <= min(pa + SW_AHEAD, p_last); ++p) issue(p);
+        for (int p = p_first; p <= min(pa + AHEAD, p_last); ++p) issue(p, p - p_first);
 
     // this thread's quad: cells x0..x0+3 of rows yA (even) and yB = yA + 1 (odd)
+    SwThread t;
+    t.lane = lane; t.sink = 0;
     const int x0 = 1 + 4 * (32 * wx + lane);
     const int rA = 1 + 2 * pr;
     const int yA = y0 - 2 + rA, yB = yA + 1;
     const bool lane_in = x0 <= g.W;
-    const bool intA = lane_in && yA >= 1 && yA <= g.H;               // row takes part in stage 0
-    const bool intB = lane_in && yB >= 1 && yB <= g.H;
-    const bool ownA = intA && pr >= 1;                               // row is stored by this CTA
-    const bool ownB = intB && pr <= NP - 2;
-    const int offA = wx * BOXF + rA * SW_BOXW + 4 * (lane + 1), offB = offA + SW_BOXW;
-    const int offLA = wx * BOXF + rA * SW_BOXW + 3, offLB = offLA + SW_BOXW;      // cell left of lane 0
-    const int offRA = offLA + 129, offRB = offLB + 129;                           // cell right of lane 31
+    t.intA = lane_in && yA >= 1 && yA <= g.H;                        // row takes part in stage 0
+    t.intB = lane_in && yB >= 1 && yB <= g.H;
+    t.ownA = t.intA && pr >= 1;                                      // row is stored by this CTA
+    t.ownB = t.intB && pr <= NP - 2;
+    t.offA = wx * BOXF + rA * SW_BOXW + 4 * (lane + 1); t.offB = t.offA + SW_BOXW;
+    t.roffA = XSLOTF + wx * RBOXF + (rA - 1) * SW_RBOXW + 4 * lane; t.roffB = t.roffA + SW_RBOXW;
+    // warp-edge lanes publish their outer cell into the neighbour column's halo, or copy the x ghosts
+    t.pub_gl = lane == 0 && wx == 0;        t.pub_nl = lane == 0 && wx > 0;
+    t.pub_gr = lane == 31 && wx == TXW - 1; t.pub_nr = lane == 31 && wx + 1 < TXW;
     const unsigned exbits = (x0 == 1 ? SW_XLO : 0u) | (x0 + 3 == g.W ? SW_XHI : 0u);
-    const unsigned eA = exbits | (yA == 1 ? SW_YLO : 0u) | (yA == g.H ? SW_YHI : 0u);
-    const unsigned eB = exbits | (yB == 1 ? SW_YLO : 0u) | (yB == g.H ? SW_YHI : 0u);
-    const long long idxA = fl_idx(g, x0, yA, 0), idxB = idxA + g.pitch;
+    t.eA = exbits | (yA == 1 ? SW_YLO : 0u) | (yA == g.H ? SW_YHI : 0u);
+    t.eB = exbits | (yB == 1 ? SW_YLO : 0u) | (yB == g.H ? SW_YHI : 0u);
+    // element offsets (32-bit: the padded volume has < 2^32 cells).  Rows / lanes outside the grid
+    // read a harmless in-range cell instead of being predicated off.
+    const unsigned plane = (unsigned)g.plane;
+    const unsigned safe = (unsigned)fl_idx(g, 1, 1, 0);
+    t.oA = (t.intA ? (unsigned)fl_idx(g, x0, yA, 0) : safe) + (unsigned)pa * plane;
+    t.oB = (t.intB ? (unsigned)fl_idx(g, x0, yB, 0) : safe) + (unsigned)pa * plane;
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { t.QA[i] = zero4; t.QB[i] = zero4; t.RA[i] = zero4; t.RB[i] = zero4; t.FA[i] = 0; t.FB[i] = 0; }
 
-    // prologue: own column of planes pa-1 (behind) and pa (centre), rhs / flags of plane pa
-    float4 z2A = zero4, z2B = zero4, mA = zero4, mB = zero4, cA, cB;
-    if (pa - 1 >= 0) { wait_plane(pa - 1); mA = sw_lds4(uslot(pa - 1) + offA); mB = sw_lds4(uslot(pa - 1) + offB); }
-    wait_plane(pa);
-    cA = sw_lds4(uslot(pa) + offA); cB = sw_lds4(uslot(pa) + offB);
-    float4 rcA = zero4, rcB = zero4, rpA = zero4, rpB = zero4;
-    unsigned fcA = 0, fcB = 0, fpA = 0, fpB = 0;
-    if (pa >= 1) {
-        const long long o = (long long)pa * g.plane;
-        if (intA) { rcA = ld4(rhs + idxA + o); fcA = *reinterpret_cast<const unsigned*>(flags + idxA + o); }
-        if (intB) { rcB = ld4(rhs + idxB + o); fcB = *reinterpret_cast<const unsigned*>(flags + idxB + o); }
-    }
+    // prologue: own column of planes pa-1 (ring index 1) and pa (index 2), flag bytes of plane pa+1
+    int sc = pa - p_first;                                           // slot of plane pa (0 or 1)
+    unsigned phase = 0;                                              // mbarrier parity of the next plane's slot
+    if (sc > 0) { sw_mbar_wait(&bars[0], 0); t.QA[1] = sw_lds4(uring + t.offA); t.QB[1] = sw_lds4(uring + t.offB); }
+    sw_mbar_wait(&bars[sc], 0);
+    const float* Up = uring + sc * SLOTF;
+    t.QA[2] = sw_lds4(Up + t.offA); t.QB[2] = sw_lds4(Up + t.offB);
+    t.FA[3] = *reinterpret_cast<const unsigned*>(A.flags + t.oA + plane);
+    t.FB[3] = *reinterpret_cast<const unsigned*>(A.flags + t.oB + plane);
     __syncthreads();        // slot of plane pa-1 is re-armed by the first iteration
 
-    for (int p = pa; p <= pb; ++p) {
-        if (tid == 0 && p + 1 + SW_AHEAD <= p_last) issue(p + 1 + SW_AHEAD);
-        // rhs / flags of plane p+1 go out first: they are consumed one iteration later
-        float4 rnA = zero4, rnB = zero4;
-        unsigned fnA = 0, fnB = 0;
-        if (p + 1 <= g.Dl) {
-            const long long o = (long long)(p + 1) * g.plane;
-            if (intA) { rnA = ld4(rhs + idxA + o); fnA = *reinterpret_cast<const unsigned*>(flags + idxA + o); }
-            if (intB) { rnB = ld4(rhs + idxB + o); fnB = *reinterpret_cast<const unsigned*>(flags + idxB + o); }
-        }
-        float4 nA = zero4, nB = zero4;
-        if (p + 1 <= p_last) {
-            wait_plane(p + 1);
-            const float* Un = uslot(p + 1);
-            nA = sw_lds4(Un + offA); nB = sw_lds4(Un + offB);
-        }
-        const float* Up = uslot(p);
-        const int E = (g.zlo + p) & 1;                               // (z_global(p) + 1) & 1
-
-        if (MODE == 0) {
-            // ---- Jacobi: relax all four lanes of plane p from the old planes p-1, p, p+1 ----------
-            if (p >= za && p <= zb) {
-                const float4 ymA = sw_lds4(Up + offA - SW_BOXW), ypB = sw_lds4(Up + offB + SW_BOXW);
-                float LA = __shfl_up_sync(0xffffffffu, cA.w, 1), RA = __shfl_down_sync(0xffffffffu, cA.x, 1);
-                float LB = __shfl_up_sync(0xffffffffu, cB.w, 1), RB = __shfl_down_sync(0xffffffffu, cB.x, 1);
-                if (lane == 0) { LA = Up[offLA]; LB = Up[offLB]; }
-                if (lane == 31) { RA = Up[offRA]; RB = Up[offRB]; }
-                const unsigned zbits = (g.zlo + p - 1 == 1 ? SW_ZLO : 0u) | (g.zlo + p - 1 == g.D ? SW_ZHI : 0u);
-                const long long o = (long long)p * g.plane;
-                if (ownA) {
-                    float4 e = cA, f = cA;
-                    sw_relax2<0>(e, LA, RA, cB, ymA, nA, mA, rcA, a, cr);
-                    sw_relax2<1>(f, LA, RA, cB, ymA, nA, mA, rcA, a, cr);
-                    sw_store(g, out, idxA + o, make_float4(e.x, f.y, e.z, f.w), fcA, b, zmask4, eA | zbits);
-                }
-                if (ownB) {
-                    float4 e = cB, f = cB;
-                    sw_relax2<0>(e, LB, RB, ypB, cA, nB, mB, rcB, a, cr);
-                    sw_relax2<1>(f, LB, RB, ypB, cA, nB, mB, rcB, a, cr);
-                    sw_store(g, out, idxB + o, make_float4(e.x, f.y, e.z, f.w), fcB, b, zmask4, eB | zbits);
-                }
-            }
-        } else {
-            // ---- stage 0: colour-0 cells of plane p, in registers ----------------------------------
-            if (p >= 1 && p <= g.Dl) {
-                const float4 ymA = sw_lds4(Up + offA - SW_BOXW), ypB = sw_lds4(Up + offB + SW_BOXW);
-                if (E == 0) {
-                    float L = __shfl_up_sync(0xffffffffu, cA.w, 1), R = __shfl_down_sync(0xffffffffu, cB.x, 1);
-                    if (lane == 0) L = Up[offLA];
-                    if (lane == 31) R = Up[offRB];
-                    if (intA) sw_relax2<0>(cA, L, 0.0f, cB, ymA, nA, mA, rcA, a, cr);
-                    if (intB) sw_relax2<1>(cB, 0.0f, R, ypB, cA, nB, mB, rcB, a, cr);
-                } else {
-                    float R = __shfl_down_sync(0xffffffffu, cA.x, 1), L = __shfl_up_sync(0xffffffffu, cB.w, 1);
-                    if (lane == 31) R = Up[offRA];
-                    if (lane == 0) L = Up[offLB];
-                    if (intA) sw_relax2<1>(cA, 0.0f, R, cB, ymA, nA, mA, rcA, a, cr);
-                    if (intB) sw_relax2<0>(cB, L, 0.0f, ypB, cA, nB, mB, rcB, a, cr);
-                }
-            }
-            // publish plane p (colour 0 new, colour 1 old) for the row / warp neighbours
-            float* Vp = vbuf + (p & 1) * SLOTF;
-            sw_sts4(Vp + offA, cA); sw_sts4(Vp + offB, cB);
-            if (lane == 0) {
-                if (wx > 0) { Vp[offRA - BOXF] = cA.x; Vp[offRB - BOXF] = cB.x; }
-                else        { Vp[offLA] = Up[offLA];   Vp[offLB] = Up[offLB]; }      // x = 0 ghosts
-            }
-            if (lane == 31) {
-                if (wx + 1 < TXW) { Vp[offLA + BOXF] = cA.w; Vp[offLB + BOXF] = cB.w; }
-                else              { Vp[offRA] = Up[offRA];   Vp[offRB] = Up[offRB]; } // x = W+1 ghosts
-            }
-            // ---- stage 1: colour-1 cells of plane p-1 from colour-0 values, then setBounds ---------
-            const int q = p - 1;
-            if (q >= za && q <= zb) {
-                const float* Vq = vbuf + (q & 1) * SLOTF;            // published (and synced) last iteration
-                const float4 ymA = sw_lds4(Vq + offA - SW_BOXW), ypB = sw_lds4(Vq + offB + SW_BOXW);
-                if (E == 0) {
-                    float L = __shfl_up_sync(0xffffffffu, mA.w, 1), R = __shfl_down_sync(0xffffffffu, mB.x, 1);
-                    if (lane == 0) L = Vq[offLA];
-                    if (lane == 31) R = Vq[offRB];
-                    if (ownA) sw_relax2<0>(mA, L, 0.0f, mB, ymA, cA, z2A, rpA, a, cr);
-                    if (ownB) sw_relax2<1>(mB, 0.0f, R, ypB, mA, cB, z2B, rpB, a, cr);
-                } else {
-                    float R = __shfl_down_sync(0xffffffffu, mA.x, 1), L = __shfl_up_sync(0xffffffffu, mB.w, 1);
-                    if (lane == 31) R = Vq[offRA];
-                    if (lane == 0) L = Vq[offLB];
-                    if (ownA) sw_relax2<1>(mA, 0.0f, R, mB, ymA, cA, z2A, rpA, a, cr);
-                    if (ownB) sw_relax2<0>(mB, L, 0.0f, ypB, mA, cB, z2B, rpB, a, cr);
-                }
-                const int gzq = g.zlo + q - 1;
-                const unsigned zbits = (gzq == 1 ? SW_ZLO : 0u) | (gzq == g.D ? SW_ZHI : 0u);
-                const long long o = (long long)q * g.plane;
-                if (ownA) sw_store(g, out, idxA + o, mA, fpA, b, zmask4, eA | zbits);
-                if (ownB) sw_store(g, out, idxB + o, mB, fpB, b, zmask4, eB | zbits);
-            }
-        }
-        // advance the register column by one plane
-        z2A = mA; z2B = mB; mA = cA; mB = cB; cA = nA; cB = nB;
-        rpA = rcA; rpB = rcB; rcA = rnA; rcB = rnB;
-        fpA = fcA; fpB = fcB; fcA = fnA; fcB = fnB;
-        sw_fence_proxy_async();        // generic-proxy reads of the slot the next TMA overwrites
-        __syncthreads();
+    int p = pa;
+    // No proxy fence before the barrier: the slot the next TMA overwrites was only READ through the
+    // generic proxy, and those reads are ordered before the issuing thread's TMA by the barrier.
+#define SW_STEP(U, E)                                                                                       \
+    {                                                                                                       \
+        if (p > pb) break;                                                                                  \
+        int sn = sc + 1; if (sn == NSLOT) { sn = 0; phase ^= 1u; }             /* slot of plane p+1 */      \
+        if (tid == 0 && p + 1 + AHEAD <= p_last) {                                                          \
+            int si = sn + AHEAD; if (si >= NSLOT) si -= NSLOT;                 /* = slot of plane p-1 */    \
+            issue(p + 1 + AHEAD, si);                                                                       \
+        }                                                                                                   \
+        t.oA += plane; t.oB += plane;                                                                       \
+        const float* Un = uring + sn * SLOTF;                                                               \
+        sw_step<BOXF, XSLOTF, MODE, U, E>(t, A, out, b, zmask4, p, za, zb, p_last, Up, Un, &bars[sn],       \
+                                          phase, vbuf);                                                     \
+        Up = Un; sc = sn; ++p;                                                                              \
+        __syncthreads();                                                                                    \
     }
+    if (((g.zlo + pa) & 1) == 0) { for (;;) { SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
+    else                         { for (;;) { SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
+#undef SW_STEP
+    if (A.zc < 0) out[0] = __uint_as_float(t.sink);                  // never taken: keeps t.sink observable
 }
 
 // ---- host side -------------------------------------------------------------------------------
@@ -339,7 +418,7 @@ typedef CUresult (*sw_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, 
 
 struct StreamState {
     sw_encode_fn encode = nullptr;
-    std::map<std::pair<const float*, int>, CUtensorMap> maps;   // (field buffer, box rows) -> 3-D tensor map
+    std::map<std::pair<const float*, int>, CUtensorMap> maps;   // (field buffer, box rows * 1024 + box width) -> 3-D tensor map
     bool attr_set = false;
     int zc_override = 0;
     int np_override = 0;
@@ -366,17 +445,17 @@ inline void fl_tiled_release(fluid_handle* h)
     h->tiled = nullptr;
 }
 
-inline int sw_get_map(fluid_handle* h, const float* buf, int box_rows, CUtensorMap* out)
+inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows, CUtensorMap* out)
 {
     StreamState* s = sw_state(h);
-    auto key = std::make_pair(buf, box_rows);
+    auto key = std::make_pair(buf, box_rows * 1024 + box_w);
     auto it = s->maps.find(key);
     if (it == s->maps.end()) {
         const Grid& g = h->g;
         CUtensorMap m;
         cuuint64_t dims[3] = { (cuuint64_t)g.pitch, (cuuint64_t)g.rows, (cuuint64_t)(g.Dl + 2) };
         cuuint64_t strides[2] = { (cuuint64_t)g.pitch * 4, (cuuint64_t)g.plane * 4 };
-        cuuint32_t box[3] = { SW_BOXW, (cuuint32_t)box_rows, 1 };
+        cuuint32_t box[3] = { (cuuint32_t)box_w, (cuuint32_t)box_rows, 1 };
         cuuint32_t estr[3] = { 1, 1, 1 };
         CUresult r = s->encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)buf, dims, strides, box, estr,
                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
@@ -432,7 +511,8 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     float* cur[3]; float* alt[3];
     for (int i = 0; i < nb; ++i) {
         cur[i] = h->field[fid[i]]; alt[i] = h->scratch[i];
-        A.rhs[i] = h->field[pid[i]]; A.b[i] = b[i];
+        A.b[i] = b[i];
+        if (int e = sw_get_map(h, h->field[pid[i]], SW_RBOXW, GE::BR - 2, &A.rmap[i])) return e;
     }
     dim3 ge((2 * (g.W + 2) + 2 * g.H + 127) / 128, g.Dl + 2);
     for (int i = 0; i < nb; ++i) {                                        // edge/corner ghosts follow
@@ -441,7 +521,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     }
     for (int k = 0; k < h->acc; ++k) {                                    // simulation.cpp:258
         for (int i = 0; i < nb; ++i) {
-            if (int e = sw_get_map(h, cur[i], GE::BR, &A.map[i])) return e;
+            if (int e = sw_get_map(h, cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
             A.dst[i] = alt[i];
         }
         if (jacobi) kj<<<grid, GE::THREADS, GE::SMEM, h->stream>>>(A);
@@ -470,7 +550,7 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
     const bool jac = solver == FLUID_SOLVER_JACOBI;
     int e;
     if (g.W <= 128)      e = sw_run<1, 16>(h, nb, b, fid, pid, a, c, jac);
-    else if (g.W <= 256) e = sw_run<2, 9>(h, nb, b, fid, pid, a, c, jac);
+    else if (g.W <= 256) e = sw_run<2, 8>(h, nb, b, fid, pid, a, c, jac);
     else                 e = sw_run<4, 4>(h, nb, b, fid, pid, a, c, jac);
     if (e) return e;
     *handled = true;
