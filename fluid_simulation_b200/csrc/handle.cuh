@@ -35,6 +35,7 @@ struct fluid_handle {
     std::vector<ProfRec> prof;
     std::vector<cudaEvent_t> ev_pool;
     int sm_count = 148;
+    size_t l2_persist_max = 0, l2_window_max = 0;   // persisting-L2 carve-out and access-window limits
 };
 
 extern thread_local std::string g_fluid_create_error;

@@ -80,15 +80,9 @@ __device__ __forceinline__ void sw_fence_proxy_async()
 {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
-// 128-bit shared load the compiler cannot split: when only two lanes of the quad are live it would
-// otherwise emit two scalar LDS, each a 4-way bank conflict across the warp (stride 16 B).
-__device__ __forceinline__ float4 sw_lds4(const float* p)
-{
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(sw_smem(p)));
-    return v;
-}
+// 128-bit shared load.  Where only two lanes of the quad are consumed the caller folds the other two
+// into a sink word (sw_lds4_half), otherwise the load is narrowed to two scalar LDS.
+__device__ __forceinline__ float4 sw_lds4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 // cell left of a quad (L) / right of it (R): the neighbour lane's outer cell by shuffle; the two
 // edge lanes of the warp read the halo column of the shared-memory box instead.
 __device__ __forceinline__ float sw_left(const float4& c, const float* row_quad, int lane)
@@ -519,6 +513,20 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         k_copy_edges<<<ge, 128, 0, h->stream>>>(g, cur[i], alt[i]);
         FL_CHECK_LAUNCH(h);
     }
+    // Single-field solves re-read the same right-hand side acc times: pin it in the persisting part of
+    // L2 for the duration of the solve so that only x streams through HBM.
+    const size_t fbytes = (size_t)g.cells * sizeof(float);
+    const bool pin = nb == 1 && h->l2_persist_max > 0 && h->acc > 1;
+    if (pin) {
+        cudaStreamAttrValue av = {};
+        av.accessPolicyWindow.base_ptr = (void*)h->field[pid[0]];
+        av.accessPolicyWindow.num_bytes = fbytes < h->l2_window_max ? fbytes : h->l2_window_max;
+        const double r = (double)h->l2_persist_max * 0.9 / (double)av.accessPolicyWindow.num_bytes;
+        av.accessPolicyWindow.hitRatio = r > 1.0 ? 1.0f : (float)r;
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        FL_CUDA(h, cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av));
+    }
     for (int k = 0; k < h->acc; ++k) {                                    // simulation.cpp:258
         for (int i = 0; i < nb; ++i) {
             if (int e = sw_get_map(h, cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
@@ -528,6 +536,11 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         else        kr<<<grid, GE::THREADS, GE::SMEM, h->stream>>>(A);
         FL_CHECK_LAUNCH(h);
         for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
+    }
+    if (pin) {
+        cudaStreamAttrValue av = {};
+        av.accessPolicyWindow.num_bytes = 0;
+        FL_CUDA(h, cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av));
     }
     for (int i = 0; i < nb; ++i)
         if (cur[i] != h->field[fid[i]]) { h->scratch[i] = h->field[fid[i]]; h->field[fid[i]] = cur[i]; }
