@@ -34,6 +34,9 @@
 #define SW_BOXW   136                    // floats per x box row: halo quad + 32 quads + halo quad
 #define SW_RBOXW  128                    // floats per rhs box row (no halo columns)
 #define SW_SMEM_MAX 232448               // 227 KB of dynamic shared memory per CTA on sm_100
+#define SW_SM_SMEM  233472               // 228 KB of shared memory per SM (each resident CTA also reserves 1 KB)
+
+struct SwSeg { int col, za, zb, pad; };     // column (batched field * row tiles + row tile), planes za..zb
 
 struct alignas(64) StreamArgs {
     CUtensorMap map[3];                  // source field of each batched solve (box SW_BOXW x BR x 1)
@@ -41,9 +44,13 @@ struct alignas(64) StreamArgs {
     float* dst[3];
     int b[3];
     const unsigned char* flags;
+    const SwSeg* segs;                   // CTA k works through segs[seg_first[k] .. seg_first[k+1])
+    const int* seg_first;
     Grid g;
     float a, c_recip;
-    int zc;                              // planes per z-chunk
+    int nty;                             // row tiles per field
+    int l2_ahead;                        // L2 prefetch distance beyond the shared-memory ring, in planes (0 = off)
+    int dbg;                             // FLUID_SW_DBG timing experiments: 1 = no stores, 2 = no relaxation (results invalid)
 };
 
 // ---- PTX wrappers (mbarrier + TMA) -----------------------------------------------------------
@@ -75,6 +82,12 @@ __device__ __forceinline__ void sw_tma_load_3d(void* dst, const CUtensorMap* map
         "[%0], [%1, {%2, %3, %4}], [%5];"
         ::"r"(sw_smem(dst)), "l"(reinterpret_cast<unsigned long long>(map)), "r"(c0), "r"(c1), "r"(c2),
           "r"(sw_smem(bar)) : "memory");
+}
+// L2-only prefetch of a box: hides the HBM latency of planes that have no shared-memory slot yet
+__device__ __forceinline__ void sw_tma_prefetch_3d(const CUtensorMap* map, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];"
+                 ::"l"(reinterpret_cast<unsigned long long>(map)), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 __device__ __forceinline__ void sw_fence_proxy_async()
 {
@@ -154,7 +167,7 @@ __device__ __forceinline__ void sw_store(const Grid& g, float* __restrict__ out,
     }
 }
 
-template <int TXW, int NP>
+template <int TXW, int NP, int CPS = 1>
 struct SwGeom {
     static constexpr int BR = 2 * NP + 2;                            // x box rows: TY owned + 2 halo + 2 read-only
     static constexpr int TY = 2 * NP - 2;                            // owned rows per CTA
@@ -166,7 +179,8 @@ struct SwGeom {
     static constexpr int TX_BYTES = TXW * (SW_BOXW * BR + SW_RBOXW * (BR - 2)) * 4;
     // ring depth: as many planes in flight as shared memory allows (the TMA ring IS the latency hiding:
     // one CTA per SM, so the bytes in flight are the bytes of the slots being filled)
-    static constexpr int NSLOT_FIT = (SW_SMEM_MAX - 2 * XSLOTF * 4 - 1024) / (SLOTF * 4);
+    static constexpr int SMEM_BUDGET = CPS == 1 ? SW_SMEM_MAX : (SW_SM_SMEM / CPS - 2048);      // per CTA
+    static constexpr int NSLOT_FIT = (SMEM_BUDGET - 2 * XSLOTF * 4 - 1024) / (SLOTF * 4);
     static constexpr int NSLOT = NSLOT_FIT > 8 ? 8 : NSLOT_FIT;
     static constexpr int AHEAD = NSLOT - 2;                          // TMA prefetch distance in planes
     static constexpr size_t SMEM = (size_t)(NSLOT * SLOTF + 2 * XSLOTF) * sizeof(float);
@@ -203,33 +217,59 @@ __device__ __forceinline__ float4 sw_lds4_half(const float* p, unsigned& sink)
     return v;
 }
 
-// one plane of the pipeline: stage 0 on plane p, stage 1 on plane p-1 (Jacobi: the whole update of
-// plane p).  U = position in the 4-step unrolled loop, E = (z_global(p) + 1) & 1, both static.
-template <int BOXF, int XSLOTF, int MODE, int U, int E>
+// one plane of the pipeline: stage 0 on plane p, stage 1 on the plane one step behind (Jacobi: the
+// whole update of plane p).  U = position in the 4-step unrolled loop, E = (z_global(p) + 1) & 1 and
+// DIR = +1 / -1 (planes streamed upwards / downwards) are static.  "next" / "behind" below are in
+// stream order; zp / zm of the relaxation are picked from them according to DIR so the operand order
+// of the reference (z+1 before z-1) is kept in both directions.
+template <int BOXF, int XSLOTF, int MODE, int DIR, int U, int E>
 __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float* __restrict__ out, int b,
-                                        unsigned zmask4, int p, int za, int zb, int p_last,
+                                        unsigned zmask4, int p, int za, int zb, bool has_next,
                                         const float* Up, const float* Un, unsigned long long* bar_n,
                                         unsigned phase_n, float* vbuf)
 {
     const Grid& g = A.g;
     const float a = A.a, cr = A.c_recip;
-    const unsigned plane = (unsigned)g.plane;
+    const unsigned dplane = DIR > 0 ? (unsigned)g.plane : 0u - (unsigned)g.plane;   // one step, mod 2^32
     constexpr int I2 = U & 3, IM = (U + 1) & 3, IC = (U + 2) & 3, IN = (U + 3) & 3;
     const int offA = t.offA, offB = t.offB;
-    // flag bytes of plane p+2 (t.oA addresses plane p+1): consumed by the store of that plane, which
-    // is three steps away for red-black and two for Jacobi
-    if (p + 2 <= zb) {
-        t.FA[I2] = *reinterpret_cast<const unsigned*>(A.flags + t.oA + plane);
-        t.FB[I2] = *reinterpret_cast<const unsigned*>(A.flags + t.oB + plane);
+    // flag bytes two steps ahead (t.oA addresses the next plane): consumed by the store of that
+    // plane, which is three steps away for red-black and two for Jacobi
+    if (p + 2 * DIR >= za && p + 2 * DIR <= zb) {
+        t.FA[I2] = *reinterpret_cast<const unsigned*>(A.flags + (t.oA + dplane));
+        t.FB[I2] = *reinterpret_cast<const unsigned*>(A.flags + (t.oB + dplane));
     }
-    // rhs of plane p sits in the slot of plane p (arrived at least one step ago)
+    // Every shared-memory operand of the step is fetched up front, in one burst, so that the LDS
+    // latency is exposed once per plane instead of once per stage: rhs and the row neighbours of plane
+    // p (TMA slot), the row neighbours of the plane behind (published last step), then the own column
+    // of the next plane as soon as its TMA has landed.
     t.RA[IC] = sw_lds4(Up + t.roffA); t.RB[IC] = sw_lds4(Up + t.roffB);
-    if (p + 1 <= p_last) {
+    float4& cA = t.QA[IC]; float4& cB = t.QB[IC];
+    const float4& mA = t.QA[IM]; const float4& mB = t.QB[IM];
+    const float* Vq = vbuf + ((U + 1) & 1) * XSLOTF;                 // published (and synced) last step
+    const int q = p - DIR;
+    const bool do0 = MODE == 1 && p >= 1 && p <= g.Dl && !(A.dbg & 2), do1 = MODE == 1 && q >= za && q <= zb && !(A.dbg & 2);
+    float4 ymA0 = cA, ypB0 = cB, ymA1 = cA, ypB1 = cB;
+    float L0 = 0.0f, R0 = 0.0f, L1 = 0.0f, R1 = 0.0f;
+    if (do0) {
+        ymA0 = sw_lds4_half<E>(Up + offA - SW_BOXW, t.sink);
+        ypB0 = sw_lds4_half<1 - E>(Up + offB + SW_BOXW, t.sink);
+        if (E == 0) { L0 = sw_left(cA, Up + offA, t.lane); R0 = sw_right(cB, Up + offB, t.lane); }
+        else        { R0 = sw_right(cA, Up + offA, t.lane); L0 = sw_left(cB, Up + offB, t.lane); }
+    }
+    if (do1) {
+        ymA1 = sw_lds4_half<E>(Vq + offA - SW_BOXW, t.sink);
+        ypB1 = sw_lds4_half<1 - E>(Vq + offB + SW_BOXW, t.sink);
+        if (E == 0) { L1 = sw_left(mA, Vq + offA, t.lane); R1 = sw_right(mB, Vq + offB, t.lane); }
+        else        { R1 = sw_right(mA, Vq + offA, t.lane); L1 = sw_left(mB, Vq + offB, t.lane); }
+    }
+    if (has_next) {
         sw_mbar_wait(bar_n, phase_n);
         t.QA[IN] = sw_lds4(Un + offA); t.QB[IN] = sw_lds4(Un + offB);
     }
-    float4& cA = t.QA[IC]; float4& cB = t.QB[IC];
-    const float4& mA = t.QA[IM]; const float4& mB = t.QB[IM];
+    // stage 0 / Jacobi at plane p: z+1 is the next plane when streaming upwards
+    const float4& zpA0 = DIR > 0 ? t.QA[IN] : mA; const float4& zmA0 = DIR > 0 ? mA : t.QA[IN];
+    const float4& zpB0 = DIR > 0 ? t.QB[IN] : mB; const float4& zmB0 = DIR > 0 ? mB : t.QB[IN];
 
     if (MODE == 0) {
         // ---- Jacobi: relax all four lanes of plane p from the old planes p-1, p, p+1 --------------
@@ -239,28 +279,24 @@ __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float*
             const float LB = sw_left(cB, Up + offB, t.lane), RB = sw_right(cB, Up + offB, t.lane);
             const unsigned zbits = (g.zlo + p - 1 == 1 ? SW_ZLO : 0u) | (g.zlo + p - 1 == g.D ? SW_ZHI : 0u);
             float4 e = cA, f = cA;
-            sw_relax2<0>(e, LA, RA, cB, ymA, t.QA[IN], mA, t.RA[IC], a, cr);
-            sw_relax2<1>(f, LA, RA, cB, ymA, t.QA[IN], mA, t.RA[IC], a, cr);
-            if (t.ownA) sw_store(g, out, t.oA - plane, make_float4(e.x, f.y, e.z, f.w), t.FA[IC], b, zmask4, t.eA | zbits);
+            sw_relax2<0>(e, LA, RA, cB, ymA, zpA0, zmA0, t.RA[IC], a, cr);
+            sw_relax2<1>(f, LA, RA, cB, ymA, zpA0, zmA0, t.RA[IC], a, cr);
+            if (t.ownA) sw_store(g, out, t.oA - dplane, make_float4(e.x, f.y, e.z, f.w), t.FA[IC], b, zmask4, t.eA | zbits);
             e = cB; f = cB;
-            sw_relax2<0>(e, LB, RB, ypB, cA, t.QB[IN], mB, t.RB[IC], a, cr);
-            sw_relax2<1>(f, LB, RB, ypB, cA, t.QB[IN], mB, t.RB[IC], a, cr);
-            if (t.ownB) sw_store(g, out, t.oB - plane, make_float4(e.x, f.y, e.z, f.w), t.FB[IC], b, zmask4, t.eB | zbits);
+            sw_relax2<0>(e, LB, RB, ypB, cA, zpB0, zmB0, t.RB[IC], a, cr);
+            sw_relax2<1>(f, LB, RB, ypB, cA, zpB0, zmB0, t.RB[IC], a, cr);
+            if (t.ownB) sw_store(g, out, t.oB - dplane, make_float4(e.x, f.y, e.z, f.w), t.FB[IC], b, zmask4, t.eB | zbits);
         }
     } else {
         // ---- stage 0: colour-0 cells of plane p, in registers --------------------------------------
-        if (p >= 1 && p <= g.Dl) {
-            const float4 ymA = sw_lds4_half<E>(Up + offA - SW_BOXW, t.sink);
-            const float4 ypB = sw_lds4_half<1 - E>(Up + offB + SW_BOXW, t.sink);
+        if (do0) {
             float4 tA = cA, tB = cB;
             if (E == 0) {
-                const float L = sw_left(cA, Up + offA, t.lane), R = sw_right(cB, Up + offB, t.lane);
-                sw_relax2<0>(tA, L, 0.0f, cB, ymA, t.QA[IN], mA, t.RA[IC], a, cr);
-                sw_relax2<1>(tB, 0.0f, R, ypB, cA, t.QB[IN], mB, t.RB[IC], a, cr);
+                sw_relax2<0>(tA, L0, 0.0f, cB, ymA0, zpA0, zmA0, t.RA[IC], a, cr);
+                sw_relax2<1>(tB, 0.0f, R0, ypB0, cA, zpB0, zmB0, t.RB[IC], a, cr);
             } else {
-                const float R = sw_right(cA, Up + offA, t.lane), L = sw_left(cB, Up + offB, t.lane);
-                sw_relax2<1>(tA, 0.0f, R, cB, ymA, t.QA[IN], mA, t.RA[IC], a, cr);
-                sw_relax2<0>(tB, L, 0.0f, ypB, cA, t.QB[IN], mB, t.RB[IC], a, cr);
+                sw_relax2<1>(tA, 0.0f, R0, cB, ymA0, zpA0, zmA0, t.RA[IC], a, cr);
+                sw_relax2<0>(tB, L0, 0.0f, ypB0, cA, zpB0, zmB0, t.RB[IC], a, cr);
             }
             if (t.intA) cA = tA;
             if (t.intB) cB = tB;
@@ -272,37 +308,38 @@ __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float*
         if (t.pub_nr) { Vp[offA + BOXF - 125] = cA.w; Vp[offB + BOXF - 125] = cB.w; }
         if (t.pub_gl) { Vp[offA - 1] = Up[offA - 1]; Vp[offB - 1] = Up[offB - 1]; }           // x = 0 ghosts
         if (t.pub_gr) { Vp[offA + 4] = Up[offA + 4]; Vp[offB + 4] = Up[offB + 4]; }           // x = W+1 ghosts
-        // ---- stage 1: colour-1 cells of plane p-1 from colour-0 values, then setBounds -------------
-        const int q = p - 1;
-        if (q >= za && q <= zb) {
-            const float* Vq = vbuf + ((U + 1) & 1) * XSLOTF;         // published (and synced) last iteration
-            const float4 ymA = sw_lds4_half<E>(Vq + offA - SW_BOXW, t.sink);
-            const float4 ypB = sw_lds4_half<1 - E>(Vq + offB + SW_BOXW, t.sink);
+        // ---- stage 1: colour-1 cells of the plane one step behind, from colour-0 values; setBounds --
+        if (do1) {
+            // around plane q: plane p is one step ahead of it, ring entry I2 one step behind it
+            const float4& zpA1 = DIR > 0 ? cA : t.QA[I2]; const float4& zmA1 = DIR > 0 ? t.QA[I2] : cA;
+            const float4& zpB1 = DIR > 0 ? cB : t.QB[I2]; const float4& zmB1 = DIR > 0 ? t.QB[I2] : cB;
             float4 tA = mA, tB = mB;
             if (E == 0) {
-                const float L = sw_left(mA, Vq + offA, t.lane), R = sw_right(mB, Vq + offB, t.lane);
-                sw_relax2<0>(tA, L, 0.0f, mB, ymA, cA, t.QA[I2], t.RA[IM], a, cr);
-                sw_relax2<1>(tB, 0.0f, R, ypB, mA, cB, t.QB[I2], t.RB[IM], a, cr);
+                sw_relax2<0>(tA, L1, 0.0f, mB, ymA1, zpA1, zmA1, t.RA[IM], a, cr);
+                sw_relax2<1>(tB, 0.0f, R1, ypB1, mA, zpB1, zmB1, t.RB[IM], a, cr);
             } else {
-                const float R = sw_right(mA, Vq + offA, t.lane), L = sw_left(mB, Vq + offB, t.lane);
-                sw_relax2<1>(tA, 0.0f, R, mB, ymA, cA, t.QA[I2], t.RA[IM], a, cr);
-                sw_relax2<0>(tB, L, 0.0f, ypB, mA, cB, t.QB[I2], t.RB[IM], a, cr);
+                sw_relax2<1>(tA, 0.0f, R1, mB, ymA1, zpA1, zmA1, t.RA[IM], a, cr);
+                sw_relax2<0>(tB, L1, 0.0f, ypB1, mA, zpB1, zmB1, t.RB[IM], a, cr);
             }
             const int gzq = g.zlo + q - 1;
             const unsigned zbits = (gzq == 1 ? SW_ZLO : 0u) | (gzq == g.D ? SW_ZHI : 0u);
-            if (t.ownA) sw_store(g, out, t.oA - 2 * plane, tA, t.FA[IM], b, zmask4, t.eA | zbits);
-            if (t.ownB) sw_store(g, out, t.oB - 2 * plane, tB, t.FB[IM], b, zmask4, t.eB | zbits);
+            if (t.ownA && !(A.dbg & 1)) sw_store(g, out, t.oA - 2u * dplane, tA, t.FA[IM], b, zmask4, t.eA | zbits);
+            if (t.ownB && !(A.dbg & 1)) sw_store(g, out, t.oB - 2u * dplane, tB, t.FB[IM], b, zmask4, t.eB | zbits);
         }
     }
 }
 
-// MODE 0 = Jacobi, 1 = red-black (colour 0 = (x+y+z) even first)
-template <int TXW, int NP, int MODE>
-__global__ void __launch_bounds__(32 * TXW * NP, 1) k_sweep_stream(const __grid_constant__ StreamArgs A)
+// MODE 0 = Jacobi, 1 = red-black (colour 0 = (x+y+z) even first); DIR = +1 streams every segment
+// upwards in z, -1 downwards.  The host alternates DIR from sweep to sweep: the planes a CTA wrote
+// last are the ones it reads first in the next sweep, while they are still in L2.
+// A CTA works through a short list of segments (column = batched field x row tile, planes za..zb);
+// the TMA ring and its mbarrier phases run on across segments.
+template <int TXW, int NP, int CPS, int MODE, int DIR>
+__global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __grid_constant__ StreamArgs A)
 {
-    using GE = SwGeom<TXW, NP>;
+    using GE = SwGeom<TXW, NP, CPS>;
     constexpr int BOXF = GE::BOXF, RBOXF = GE::RBOXF, SLOTF = GE::SLOTF, XSLOTF = GE::XSLOTF;
-    constexpr int NSLOT = GE::NSLOT, AHEAD = GE::AHEAD;
+    constexpr int NSLOT = GE::NSLOT;
     extern __shared__ __align__(128) float sw_mem[];
     __shared__ unsigned long long bars[NSLOT];
     float* const uring = sw_mem;                                     // NSLOT TMA slots (x boxes + rhs boxes)
@@ -311,97 +348,129 @@ __global__ void __launch_bounds__(32 * TXW * NP, 1) k_sweep_stream(const __grid_
     const Grid& g = A.g;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wx = warp % TXW, pr = warp / TXW;
-    const int batch = blockIdx.z;
-    const int y0 = 1 + blockIdx.x * GE::TY;                          // first owned row (odd)
-    const int za = 1 + blockIdx.y * A.zc;
-    const int zb = min(za + A.zc - 1, g.Dl);
-    const int pa = za - 1, pb = zb + 1;                              // stage-0 plane range
-    const int p_first = max(pa - 1, 0), p_last = min(pb + 1, g.Dl + 1);
-    const int b = A.b[batch];
-    const unsigned zmask4 = fl_zero_mask(b) * 0x01010101u;
-    float* __restrict__ out = A.dst[batch];
-
-    auto issue = [&](int p, int s) {                                 // plane p -> ring slot s
-        sw_mbar_expect_tx(&bars[s], GE::TX_BYTES);
-        float* slot = uring + s * SLOTF;
-#pragma unroll
-        for (int i = 0; i < TXW; ++i) {
-            sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p, &bars[s]);
-            sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p, &bars[s]);
-        }
-    };
 
     if (tid == 0) {
         for (int i = 0; i < NSLOT; ++i) sw_mbar_init(&bars[i], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    // ring slot of plane p is (p - p_first) mod NSLOT; the first NSLOT planes go out at once
-    if (tid == 0)
-        for (int p = p_first; p <= min(pa + AHEAD, p_last); ++p) issue(p, p - p_first);
 
-    // this thread's quad: cells x0..x0+3 of rows yA (even) and yB = yA + 1 (odd)
+    // what is constant for the thread across segments
     SwThread t;
     t.lane = lane; t.sink = 0;
     const int x0 = 1 + 4 * (32 * wx + lane);
     const int rA = 1 + 2 * pr;
-    const int yA = y0 - 2 + rA, yB = yA + 1;
     const bool lane_in = x0 <= g.W;
-    t.intA = lane_in && yA >= 1 && yA <= g.H;                        // row takes part in stage 0
-    t.intB = lane_in && yB >= 1 && yB <= g.H;
-    t.ownA = t.intA && pr >= 1;                                      // row is stored by this CTA
-    t.ownB = t.intB && pr <= NP - 2;
     t.offA = wx * BOXF + rA * SW_BOXW + 4 * (lane + 1); t.offB = t.offA + SW_BOXW;
     t.roffA = XSLOTF + wx * RBOXF + (rA - 1) * SW_RBOXW + 4 * lane; t.roffB = t.roffA + SW_RBOXW;
     // warp-edge lanes publish their outer cell into the neighbour column's halo, or copy the x ghosts
     t.pub_gl = lane == 0 && wx == 0;        t.pub_nl = lane == 0 && wx > 0;
     t.pub_gr = lane == 31 && wx == TXW - 1; t.pub_nr = lane == 31 && wx + 1 < TXW;
     const unsigned exbits = (x0 == 1 ? SW_XLO : 0u) | (x0 + 3 == g.W ? SW_XHI : 0u);
-    t.eA = exbits | (yA == 1 ? SW_YLO : 0u) | (yA == g.H ? SW_YHI : 0u);
-    t.eB = exbits | (yB == 1 ? SW_YLO : 0u) | (yB == g.H ? SW_YHI : 0u);
-    // element offsets (32-bit: the padded volume has < 2^32 cells).  Rows / lanes outside the grid
-    // read a harmless in-range cell instead of being predicated off.
     const unsigned plane = (unsigned)g.plane;
+    const unsigned dplane = DIR > 0 ? plane : 0u - plane;
     const unsigned safe = (unsigned)fl_idx(g, 1, 1, 0);
-    t.oA = (t.intA ? (unsigned)fl_idx(g, x0, yA, 0) : safe) + (unsigned)pa * plane;
-    t.oB = (t.intB ? (unsigned)fl_idx(g, x0, yB, 0) : safe) + (unsigned)pa * plane;
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+
+    int s_iss = 0;                                                   // ring slot the next TMA plane goes to
+    int s_con = 0; unsigned ph_con = 0;                              // slot / mbarrier parity of the next plane consumed
+
+    for (int si = A.seg_first[blockIdx.x]; si < A.seg_first[blockIdx.x + 1]; ++si) {
+        const SwSeg sg = A.segs[si];
+        const int batch = sg.col / A.nty;
+        const int y0 = 1 + (sg.col - batch * A.nty) * GE::TY;        // first owned row (odd)
+        const int za = sg.za, zb = sg.zb;
+        const int lo = max(za - 2, 0), hi = min(zb + 2, g.Dl + 1);   // planes this segment reads
+        const int ps = DIR > 0 ? za - 1 : zb + 1;                    // first stage-0 plane
+        const int nsteps = zb - za + 3;
+        const bool has_behind = DIR > 0 ? (ps - 1 >= lo) : (ps + 1 <= hi);
+        const int first = has_behind ? ps - DIR : ps;                // first plane loaded, then first + DIR, ...
+        const int nplanes = (DIR > 0 ? hi - first : first - lo) + 1;
+        const int b = A.b[batch];
+        const unsigned zmask4 = fl_zero_mask(b) * 0x01010101u;
+        float* __restrict__ out = A.dst[batch];
+
+        auto issue = [&](int p) {                                    // plane p -> ring slot s_iss
+            unsigned long long* bar = &bars[s_iss];
+            sw_mbar_expect_tx(bar, GE::TX_BYTES);
+            float* slot = uring + s_iss * SLOTF;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { t.QA[i] = zero4; t.QB[i] = zero4; t.RA[i] = zero4; t.RB[i] = zero4; t.FA[i] = 0; t.FB[i] = 0; }
+            for (int i = 0; i < TXW; ++i) {
+                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p, bar);
+                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p, bar);
+            }
+            if (++s_iss == NSLOT) s_iss = 0;
+            // ... and the plane SW_L2_AHEAD steps further on starts its way from HBM into L2
+            const int pf = p + DIR * A.l2_ahead;
+            if (A.l2_ahead > 0 && pf >= lo && pf <= hi) {
+#pragma unroll
+                for (int i = 0; i < TXW; ++i) {
+                    sw_tma_prefetch_3d(&A.map[batch], 128 * i, y0 - 2, pf);
+                    sw_tma_prefetch_3d(&A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, pf);
+                }
+            }
+        };
+        int issued = min(nplanes, NSLOT);                            // planes handed to TMA so far (uniform)
+        if (tid == 0)
+            for (int j = 0; j < issued; ++j) issue(first + DIR * j);
 
-    // prologue: own column of planes pa-1 (ring index 1) and pa (index 2), flag bytes of plane pa+1
-    int sc = pa - p_first;                                           // slot of plane pa (0 or 1)
-    unsigned phase = 0;                                              // mbarrier parity of the next plane's slot
-    if (sc > 0) { sw_mbar_wait(&bars[0], 0); t.QA[1] = sw_lds4(uring + t.offA); t.QB[1] = sw_lds4(uring + t.offB); }
-    sw_mbar_wait(&bars[sc], 0);
-    const float* Up = uring + sc * SLOTF;
-    t.QA[2] = sw_lds4(Up + t.offA); t.QB[2] = sw_lds4(Up + t.offB);
-    t.FA[3] = *reinterpret_cast<const unsigned*>(A.flags + t.oA + plane);
-    t.FB[3] = *reinterpret_cast<const unsigned*>(A.flags + t.oB + plane);
-    __syncthreads();        // slot of plane pa-1 is re-armed by the first iteration
+        // this thread's quad: cells x0..x0+3 of rows yA (even) and yB = yA + 1 (odd)
+        const int yA = y0 - 2 + rA, yB = yA + 1;
+        t.intA = lane_in && yA >= 1 && yA <= g.H;                    // row takes part in stage 0
+        t.intB = lane_in && yB >= 1 && yB <= g.H;
+        t.ownA = t.intA && pr >= 1;                                  // row is stored by this CTA
+        t.ownB = t.intB && pr <= NP - 2;
+        t.eA = exbits | (yA == 1 ? SW_YLO : 0u) | (yA == g.H ? SW_YHI : 0u);
+        t.eB = exbits | (yB == 1 ? SW_YLO : 0u) | (yB == g.H ? SW_YHI : 0u);
+        // element offsets (32-bit: the padded volume has < 2^32 cells).  Rows / lanes outside the
+        // grid read a harmless in-range cell instead of being predicated off.
+        t.oA = (t.intA ? (unsigned)fl_idx(g, x0, yA, 0) : safe) + (unsigned)ps * plane;
+        t.oB = (t.intB ? (unsigned)fl_idx(g, x0, yB, 0) : safe) + (unsigned)ps * plane;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { t.QA[i] = zero4; t.QB[i] = zero4; t.RA[i] = zero4; t.RB[i] = zero4; t.FA[i] = 0; t.FB[i] = 0; }
 
-    int p = pa;
-    // No proxy fence before the barrier: the slot the next TMA overwrites was only READ through the
-    // generic proxy, and those reads are ordered before the issuing thread's TMA by the barrier.
+        // prologue: own column of the plane behind ps (ring index 1) and of ps (index 2); flag bytes
+        // of the first plane that is stored
+        auto consume = [&]() -> const float* {                       // wait for the next plane in stream order
+            sw_mbar_wait(&bars[s_con], ph_con);
+            const float* s = uring + s_con * SLOTF;
+            if (++s_con == NSLOT) { s_con = 0; ph_con ^= 1u; }
+            return s;
+        };
+        if (has_behind) { const float* Ub = consume(); t.QA[1] = sw_lds4(Ub + t.offA); t.QB[1] = sw_lds4(Ub + t.offB); }
+        const float* Up = consume();
+        t.QA[2] = sw_lds4(Up + t.offA); t.QB[2] = sw_lds4(Up + t.offB);
+        t.FA[3] = *reinterpret_cast<const unsigned*>(A.flags + (t.oA + dplane));
+        t.FB[3] = *reinterpret_cast<const unsigned*>(A.flags + (t.oB + dplane));
+        __syncthreads();        // the slot of the plane behind ps is re-armed by the first step
+
+        int p = ps, step = 0;
+        int jc = has_behind ? 1 : 0;                                 // stream index of plane p
+        // No proxy fence before the barrier: the slot the next TMA overwrites was only READ through
+        // the generic proxy, and those reads are ordered before the issuing thread's TMA by the barrier.
 #define SW_STEP(U, E)                                                                                       \
-    {                                                                                                       \
-        if (p > pb) break;                                                                                  \
-        int sn = sc + 1; if (sn == NSLOT) { sn = 0; phase ^= 1u; }             /* slot of plane p+1 */      \
-        if (tid == 0 && p + 1 + AHEAD <= p_last) {                                                          \
-            int si = sn + AHEAD; if (si >= NSLOT) si -= NSLOT;                 /* = slot of plane p-1 */    \
-            issue(p + 1 + AHEAD, si);                                                                       \
-        }                                                                                                   \
-        t.oA += plane; t.oB += plane;                                                                       \
-        const float* Un = uring + sn * SLOTF;                                                               \
-        sw_step<BOXF, XSLOTF, MODE, U, E>(t, A, out, b, zmask4, p, za, zb, p_last, Up, Un, &bars[sn],       \
-                                          phase, vbuf);                                                     \
-        Up = Un; sc = sn; ++p;                                                                              \
-        __syncthreads();                                                                                    \
-    }
-    if (((g.zlo + pa) & 1) == 0) { for (;;) { SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
-    else                         { for (;;) { SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
+        {                                                                                                   \
+            if (step == nsteps) break;                                                                      \
+            if (issued < nplanes && issued - jc < NSLOT) {        /* a slot behind plane p is free */       \
+                if (tid == 0) issue(first + DIR * issued);                                                  \
+                ++issued;                                                                                   \
+            }                                                                                               \
+            t.oA += dplane; t.oB += dplane;                                                                 \
+            const bool has_next = DIR > 0 ? (p + 1 <= hi) : (p - 1 >= lo);                                  \
+            unsigned long long* bar_n = &bars[s_con];                                                       \
+            const unsigned ph_n = ph_con;                                                                   \
+            const float* Un = uring + s_con * SLOTF;                                                        \
+            if (has_next) { if (++s_con == NSLOT) { s_con = 0; ph_con ^= 1u; } }                            \
+            sw_step<BOXF, XSLOTF, MODE, DIR, U, E>(t, A, out, b, zmask4, p, za, zb, has_next, Up, Un, bar_n, \
+                                                   ph_n, vbuf);                                             \
+            Up = Un; p += DIR; ++step; ++jc;                                                                \
+            __syncthreads();                                                                                \
+        }
+        if (((g.zlo + ps) & 1) == 0) { for (;;) { SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
+        else                         { for (;;) { SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
 #undef SW_STEP
-    if (A.zc < 0) out[0] = __uint_as_float(t.sink);                  // never taken: keeps t.sink observable
+    }
+    if (A.nty < 0) A.dst[0][0] = __uint_as_float(t.sink);            // never taken: keeps t.sink observable
 }
 
 // ---- host side -------------------------------------------------------------------------------
@@ -410,12 +479,17 @@ typedef CUresult (*sw_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, 
                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
                                  CUtensorMapFloatOOBfill);
 
+struct SwPlan {                            // segment table of one (fields, row tiles) decomposition, on the device
+    SwSeg* segs = nullptr; int* seg_first = nullptr; int nctas = 0;
+};
+
 struct StreamState {
     sw_encode_fn encode = nullptr;
     std::map<std::pair<const float*, int>, CUtensorMap> maps;   // (field buffer, box rows * 1024 + box width) -> 3-D tensor map
-    bool attr_set = false;
+    std::map<std::pair<int, int>, SwPlan> plans;                // (fields, owned rows per tile) -> segment table
     int zc_override = 0;
-    int np_override = 0;
+    bool zigzag = true, unbatch = false;
+    int cfg = 0, dbg = 0, l2_ahead = 0;
 };
 
 inline StreamState* sw_state(fluid_handle* h)
@@ -428,6 +502,11 @@ inline StreamState* sw_state(fluid_handle* h)
             qres == cudaDriverEntryPointSuccess)
             s->encode = (sw_encode_fn)fn;
         if (const char* e = getenv("FLUID_TILED_ZC")) s->zc_override = atoi(e);
+        if (const char* e = getenv("FLUID_SW_ZIGZAG")) s->zigzag = atoi(e) != 0;
+        if (const char* e = getenv("FLUID_SW_UNBATCH")) s->unbatch = atoi(e) != 0;
+        if (const char* e = getenv("FLUID_SW_CFG")) s->cfg = atoi(e);
+        if (const char* e = getenv("FLUID_SW_DBG")) s->dbg = atoi(e);
+        if (const char* e = getenv("FLUID_SW_L2AHEAD")) s->l2_ahead = atoi(e);
         h->tiled = s;
     }
     return (StreamState*)h->tiled;
@@ -435,7 +514,9 @@ inline StreamState* sw_state(fluid_handle* h)
 
 inline void fl_tiled_release(fluid_handle* h)
 {
-    delete (StreamState*)h->tiled;
+    StreamState* s = (StreamState*)h->tiled;
+    if (s) for (auto& kv : s->plans) { cudaFree(kv.second.segs); cudaFree(kv.second.seg_first); }
+    delete s;
     h->tiled = nullptr;
 }
 
@@ -461,46 +542,96 @@ inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows
     return 0;
 }
 
-// z-chunking: CTAs are (row tiles) x (z chunks) x (batched fields), one CTA per SM.  Pick the chunk
-// count whose last wave is best filled, discounted by the 4 extra planes each chunk re-reads.
-inline int sw_pick_chunks(int ctas_per_chunk, int Dl, int sms)
+// Work decomposition.  The unit of work is one plane of one column (column = batched field x row
+// tile); the ncol * Dl units, in (column, z) order, are cut into one contiguous range per SM, so
+// every SM streams the same number of planes (+-1) whatever the tile count.  A range that crosses a
+// column boundary becomes two segments; cuts closer than SW_MINSEG planes to a column boundary are
+// snapped onto it, because every segment pays 4 extra pipeline steps.
+#define SW_MINSEG 5
+#define SW_SEGCOST 4
+inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, SwPlan* out)
 {
-    int best = 1; double best_eff = -1.0;
-    for (int n = 1; n <= Dl; ++n) {
-        const int zc = (Dl + n - 1) / n;
-        if (n > 1 && zc < 6) break;
-        const int nn = (Dl + zc - 1) / zc;
-        const long long total = (long long)ctas_per_chunk * nn;
-        const long long waves = (total + sms - 1) / sms;
-        // time ~ waves * (zc + 4) planes; useful work = Dl planes per row tile
-        const double eff = (double)Dl / ((double)waves * sms / ctas_per_chunk * (zc + 4));
-        if (eff > best_eff + 1e-9) { best_eff = eff; best = nn; }
-        if (total > 8LL * sms) break;
+    StreamState* s = sw_state(h);
+    auto key = std::make_pair(nb, ty * 16 + cps);
+    auto it = s->plans.find(key);
+    if (it == s->plans.end()) {
+        const Grid& g = h->g;
+        const int nty = (g.H + ty - 1) / ty, ncol = nb * nty, Dl = g.Dl;
+        const long long T = (long long)ncol * Dl;
+        std::vector<SwSeg> segs; std::vector<int> first;
+        if (s->zc_override > 0) {                        // tests: fixed chunk height, one CTA per segment
+            const int zc = s->zc_override;
+            for (int c = 0; c < ncol; ++c)
+                for (int za = 1; za <= Dl; za += zc) {
+                    first.push_back((int)segs.size());
+                    segs.push_back(SwSeg{ c, za, za + zc - 1 < Dl ? za + zc - 1 : Dl, 0 });
+                }
+        } else {
+            long long nc = (long long)h->sm_count * cps;
+            if (nc > T / 8) nc = T / 8;                  // tiny grids: at least 8 planes per CTA
+            if (nc < 1) nc = 1;
+            // every CTA gets the same budget of pipeline steps: planes + SW_SEGCOST per segment it
+            // starts.  The smallest budget with which nc CTAs cover all columns is found by bisection.
+            auto build = [&](long long budget, bool emit) -> bool {
+                int c = 0, z = 0;
+                for (long long k = 0; k < nc; ++k) {
+                    if (emit) first.push_back((int)segs.size());
+                    long long left = budget;
+                    while (c < ncol) {
+                        const int rem = Dl - z;
+                        long long take = left - SW_SEGCOST < rem ? left - SW_SEGCOST : rem;
+                        if (rem - take > 0 && rem - take < SW_MINSEG) take = rem;       // no tiny leftovers
+                        if (take < SW_MINSEG && take < rem) break;                      // no tiny starts
+                        if (take <= 0) break;
+                        if (emit) segs.push_back(SwSeg{ c, z + 1, z + (int)take, 0 });
+                        left -= take + SW_SEGCOST; z += (int)take;
+                        if (z == Dl) { ++c; z = 0; }
+                    }
+                }
+                return c == ncol;
+            };
+            long long lo_b = T / nc, hi_b = T / nc + 3 * SW_SEGCOST + 2 * SW_MINSEG + Dl;
+            while (!build(hi_b, false)) hi_b *= 2;
+            while (lo_b + 1 < hi_b) {
+                const long long mid = (lo_b + hi_b) / 2;
+                if (build(mid, false)) hi_b = mid; else lo_b = mid;
+            }
+            build(hi_b, true);
+        }
+        first.push_back((int)segs.size());
+        SwPlan pl;
+        pl.nctas = (int)first.size() - 1;
+        FL_CUDA(h, cudaMalloc(&pl.segs, segs.size() * sizeof(SwSeg)));
+        FL_CUDA(h, cudaMalloc(&pl.seg_first, first.size() * sizeof(int)));
+        FL_CUDA(h, cudaMemcpyAsync(pl.segs, segs.data(), segs.size() * sizeof(SwSeg), cudaMemcpyHostToDevice, h->stream));
+        FL_CUDA(h, cudaMemcpyAsync(pl.seg_first, first.data(), first.size() * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+        FL_CUDA(h, cudaStreamSynchronize(h->stream));    // the host vectors go out of scope
+        it = s->plans.emplace(key, pl).first;
     }
-    return best;
+    *out = it->second;
+    return 0;
 }
 
-template <int TXW, int NP>
+template <int TXW, int NP, int CPS>
 inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
                   bool jacobi)
 {
-    using GE = SwGeom<TXW, NP>;
+    using GE = SwGeom<TXW, NP, CPS>;
     const Grid& g = h->g;
     StreamState* s = sw_state(h);
-    auto kj = k_sweep_stream<TXW, NP, 0>;
-    auto kr = k_sweep_stream<TXW, NP, 1>;
-    FL_CUDA(h, cudaFuncSetAttribute(kj, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
-    FL_CUDA(h, cudaFuncSetAttribute(kr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
+    auto kju = k_sweep_stream<TXW, NP, CPS, 0, 1>; auto kjd = k_sweep_stream<TXW, NP, CPS, 0, -1>;
+    auto kru = k_sweep_stream<TXW, NP, CPS, 1, 1>; auto krd = k_sweep_stream<TXW, NP, CPS, 1, -1>;
+    FL_CUDA(h, cudaFuncSetAttribute(kju, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
+    FL_CUDA(h, cudaFuncSetAttribute(kjd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
+    FL_CUDA(h, cudaFuncSetAttribute(kru, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
+    FL_CUDA(h, cudaFuncSetAttribute(krd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
+    SwPlan plan;
+    if (int e = sw_get_plan(h, nb, GE::TY, CPS, &plan)) return e;
     StreamArgs A;
     A.g = g; A.a = a; A.c_recip = 1.0f / c; A.flags = h->cflags;         // simulation.cpp:257
-    const int nty = (g.H + GE::TY - 1) / GE::TY;
-    int nchunks = sw_pick_chunks(nty * nb, g.Dl, h->sm_count);
-    int zc = (g.Dl + nchunks - 1) / nchunks;
-    if (s->zc_override > 0) zc = s->zc_override;
-    if (zc > g.Dl) zc = g.Dl;
-    nchunks = (g.Dl + zc - 1) / zc;
-    A.zc = zc;
-    dim3 grid(nty, nchunks, nb);
+    A.nty = (g.H + GE::TY - 1) / GE::TY;
+    A.segs = plan.segs; A.seg_first = plan.seg_first;
+    A.dbg = s->dbg; A.l2_ahead = s->l2_ahead;
 
     float* cur[3]; float* alt[3];
     for (int i = 0; i < nb; ++i) {
@@ -513,8 +644,8 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         k_copy_edges<<<ge, 128, 0, h->stream>>>(g, cur[i], alt[i]);
         FL_CHECK_LAUNCH(h);
     }
-    // Single-field solves re-read the same right-hand side acc times: pin it in the persisting part of
-    // L2 for the duration of the solve so that only x streams through HBM.
+    // Single-field solves re-read the same right-hand side acc times: optionally pin it in the
+    // persisting part of L2 (off by default, see fluid_create).
     const size_t fbytes = (size_t)g.cells * sizeof(float);
     const bool pin = nb == 1 && h->l2_persist_max > 0 && h->acc > 1;
     if (pin) {
@@ -532,8 +663,9 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
             if (int e = sw_get_map(h, cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
             A.dst[i] = alt[i];
         }
-        if (jacobi) kj<<<grid, GE::THREADS, GE::SMEM, h->stream>>>(A);
-        else        kr<<<grid, GE::THREADS, GE::SMEM, h->stream>>>(A);
+        const bool down = s->zigzag && (k & 1);          // odd sweeps stream downwards (L2 reuse)
+        auto kern = jacobi ? (down ? kjd : kju) : (down ? krd : kru);
+        kern<<<plan.nctas, GE::THREADS, GE::SMEM, h->stream>>>(A);
         FL_CHECK_LAUNCH(h);
         for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
     }
@@ -561,11 +693,21 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
     StreamState* s = sw_state(h);
     if (!s->encode) return fl_fail(h, FLUID_E_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
     const bool jac = solver == FLUID_SOLVER_JACOBI;
-    int e;
-    if (g.W <= 128)      e = sw_run<1, 16>(h, nb, b, fid, pid, a, c, jac);
-    else if (g.W <= 256) e = sw_run<2, 8>(h, nb, b, fid, pid, a, c, jac);
-    else                 e = sw_run<4, 4>(h, nb, b, fid, pid, a, c, jac);
-    if (e) return e;
+    // batched fields either go out as one launch per sweep, or (FLUID_SW_UNBATCH=1) one field after
+    // the other so that a sweep's footprint is a third as large and more of it is still in L2
+    const int ngroups = (s->unbatch && nb > 1) ? nb : 1, per = nb / ngroups;
+    for (int gi = 0; gi < ngroups; ++gi) {
+        const int* bb = b + gi * per; const int* ff = fid + gi * per; const int* pp = pid + gi * per;
+        int e;
+        if (g.W <= 128)      e = sw_run<1, 16, 1>(h, per, bb, ff, pp, a, c, jac);
+        else if (g.W <= 256) {
+            if (s->cfg == 1)      e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac);
+            else if (s->cfg == 2) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac);
+            else if (s->cfg == 3) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac);
+            else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac);
+        } else                 e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac);
+        if (e) return e;
+    }
     *handled = true;
     return 0;
 }

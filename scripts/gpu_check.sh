@@ -15,7 +15,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -s 1500 -c 700 --csv \
     --log-file $OUT/launches.csv $BENCH > $OUT/ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
 $BENCH > $OUT/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:k_sweep_tiled -s 600 -c 3 \
+ncu --set full --clock-control none --import-source on -k regex:k_sweep_stream -s 300 -c 2 \
     -o $OUT/prof_sweep $BENCH > $OUT/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la $OUT
