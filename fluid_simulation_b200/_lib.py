@@ -46,6 +46,11 @@ SYMBOLS = {
     "fluid_launch_count": (C.c_longlong, [_p]),
     "fluid_version": (C.c_char_p, []),
     "fluid_set_device": (_i, [_i]),
+    "fluid_comm_unique_id": (_i, [C.c_char_p, C.c_char_p]),
+    "fluid_comm_init": (_i, [_p, C.c_char_p, C.c_char_p]),
+    "fluid_ipc_export": (_i, [_p, _i, C.c_char_p]),
+    "fluid_ipc_import": (_i, [_p, _i, _i, C.c_char_p]),
+    "fluid_barrier": (_i, [_p]),
 }
 
 _lib = None

@@ -8,9 +8,14 @@ static int check_field(fluid_handle* h, int id, const char* who)
     return 0;
 }
 
-// offset (floats) of this slab's first local plane (zl = 0) inside the GLOBAL reference volume
-static size_t slab_host_offset(const fluid_handle* h) { return ref_plane_floats(h->g) * (size_t)(h->g.zlo - 1); }
-static size_t slab_host_floats(const fluid_handle* h) { return ref_plane_floats(h->g) * (size_t)(h->g.Dl + 2); }
+// offset (floats) of local plane zl inside the GLOBAL reference volume
+static size_t slab_host_offset(const fluid_handle* h, int zl) { return ref_plane_floats(h->g) * (size_t)(h->g.zlo - 1 + zl); }
+// planes a slab holds data for (uploads fill all of them, halos included) ...
+static int held_first(const fluid_handle* h) { return h->g.zl_lo; }
+static int held_count(const fluid_handle* h) { return h->g.zl_hi - h->g.zl_lo + 1; }
+// ... and the planes it OWNS (interior planes plus the global ghost plane(s) of the end slabs)
+static int own_first(const fluid_handle* h) { return h->rank == 0 ? 0 : 1; }
+static int own_count(const fluid_handle* h) { return (h->rank == h->nranks - 1 ? h->g.Dl + 1 : h->g.Dl) - own_first(h) + 1; }
 
 extern "C" {
 
@@ -18,10 +23,11 @@ int fluid_upload_field(fluid_handle* h, int field_id, const float* padded_host)
 {
     if (int e = check_field(h, field_id, "fluid_upload_field")) return e;
     if (!padded_host) return fl_fail(h, FLUID_E_ARG, "fluid_upload_field: null host pointer");
-    FL_CUDA(h, cudaMemcpyAsync(h->staging, padded_host + slab_host_offset(h),
-                               slab_host_floats(h) * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-    k_unpack<<<fl_grid_1d((long long)slab_host_floats(h)), 256, 0, h->stream>>>(h->g, h->staging,
-                                                                                 h->field[field_id]);
+    const size_t pf = ref_plane_floats(h->g);
+    const int zf = held_first(h), np = held_count(h);
+    FL_CUDA(h, cudaMemcpyAsync(h->staging, padded_host + slab_host_offset(h, zf), pf * np * sizeof(float),
+                               cudaMemcpyHostToDevice, h->stream));
+    k_unpack<<<fl_grid_1d((long long)(pf * np)), 256, 0, h->stream>>>(h->g, zf, np, h->staging, h->field[field_id]);
     FL_CHECK_LAUNCH(h);
     if (field_id == FLUID_OBS) h->flags_dirty = true;
     // the staging buffer is reused by the next transfer: keep host-visible ordering simple
@@ -33,16 +39,13 @@ int fluid_download_field(fluid_handle* h, int field_id, float* padded_host)
 {
     if (int e = check_field(h, field_id, "fluid_download_field")) return e;
     if (!padded_host) return fl_fail(h, FLUID_E_ARG, "fluid_download_field: null host pointer");
-    k_pack<<<fl_grid_1d((long long)slab_host_floats(h)), 256, 0, h->stream>>>(h->g, h->field[field_id],
-                                                                               h->staging);
-    FL_CHECK_LAUNCH(h);
     // a slab returns its OWNED planes only: interior planes plus the global ghost plane(s) it holds
     const size_t pf = ref_plane_floats(h->g);
-    const int first = (h->rank == 0) ? 0 : 1;
-    const int last = (h->rank == h->nranks - 1) ? h->g.Dl + 1 : h->g.Dl;
-    FL_CUDA(h, cudaMemcpyAsync(padded_host + slab_host_offset(h) + pf * first, h->staging + pf * first,
-                               pf * (size_t)(last - first + 1) * sizeof(float), cudaMemcpyDeviceToHost,
-                               h->stream));
+    const int zf = own_first(h), np = own_count(h);
+    k_pack<<<fl_grid_1d((long long)(pf * np)), 256, 0, h->stream>>>(h->g, zf, np, h->field[field_id], h->staging);
+    FL_CHECK_LAUNCH(h);
+    FL_CUDA(h, cudaMemcpyAsync(padded_host + slab_host_offset(h, zf), h->staging, pf * np * sizeof(float),
+                               cudaMemcpyDeviceToHost, h->stream));
     FL_CUDA(h, cudaStreamSynchronize(h->stream));
     return 0;
 }
@@ -121,26 +124,24 @@ int fluid_dump_frame_async(fluid_handle* h, float* const dst[5])
 {
     if (!h || !dst) return FLUID_E_ARG;
     static const int ids[5] = { FLUID_DENS, FLUID_OBS, FLUID_VX, FLUID_VY, FLUID_VZ };
-    const size_t nfl = slab_host_floats(h);
+    const size_t pf = ref_plane_floats(h->g);
+    const int zf = own_first(h), np = own_count(h);
+    const size_t nfl = pf * np;
     for (int i = 0; i < 5; ++i)
         if (dst[i] && !h->frame_staging[i]) FL_CUDA(h, cudaMalloc(&h->frame_staging[i], nfl * sizeof(float)));
     // the previous dump must have left the staging buffers before they are overwritten
     if (h->frame_in_flight) FL_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_frame_done, 0));
     for (int i = 0; i < 5; ++i) {
         if (!dst[i]) continue;
-        k_pack<<<fl_grid_1d((long long)nfl), 256, 0, h->stream>>>(h->g, h->field[ids[i]], h->frame_staging[i]);
+        k_pack<<<fl_grid_1d((long long)nfl), 256, 0, h->stream>>>(h->g, zf, np, h->field[ids[i]], h->frame_staging[i]);
         FL_CHECK_LAUNCH(h);
     }
     FL_CUDA(h, cudaEventRecord(h->ev_frame_packed, h->stream));
     FL_CUDA(h, cudaStreamWaitEvent(h->dump_stream, h->ev_frame_packed, 0));
-    const size_t pf = ref_plane_floats(h->g);
-    const int first = (h->rank == 0) ? 0 : 1;
-    const int last = (h->rank == h->nranks - 1) ? h->g.Dl + 1 : h->g.Dl;
     for (int i = 0; i < 5; ++i) {
         if (!dst[i]) continue;
-        FL_CUDA(h, cudaMemcpyAsync(dst[i] + slab_host_offset(h) + pf * first, h->frame_staging[i] + pf * first,
-                                   pf * (size_t)(last - first + 1) * sizeof(float), cudaMemcpyDeviceToHost,
-                                   h->dump_stream));
+        FL_CUDA(h, cudaMemcpyAsync(dst[i] + slab_host_offset(h, zf), h->frame_staging[i], nfl * sizeof(float),
+                                   cudaMemcpyDeviceToHost, h->dump_stream));
     }
     FL_CUDA(h, cudaEventRecord(h->ev_frame_done, h->dump_stream));
     h->frame_in_flight = true;

@@ -1,25 +1,6 @@
 // api_ops.inl -- fluid_step / fluid_call and the slab-mode hooks.  Included by fluid_cuda.cu.
 
-// ---- slab-mode hooks (multi-GPU z-slabs) ---------------------------------------
-// Single-GPU handles never reach these with nranks > 1.
-int fl_halo_exchange(fluid_handle* h, int n, float* const* fields)
-{
-    (void)n; (void)fields;
-    if (h->nranks == 1) return 0;
-    return fl_fail(h, FLUID_E_COMM, "halo exchange: no communicator attached to this slab handle");
-}
-
-void fl_comm_release(fluid_handle* h) { (void)h; }
-
-int fl_gather_sources(fluid_handle* h, int prev_id, GatherSrc* out)
-{
-    if (h->nranks == 1) {
-        out->n = 1; out->base[0] = h->field[prev_id]; out->zlo[0] = h->g.zlo; out->dl[0] = h->g.Dl;
-        return 0;
-    }
-    return fl_fail(h, FLUID_E_COMM, "advect: slab gather sources not attached");
-}
-
+// ---- slab-mode entry points (multi-GPU z-slabs); the mechanisms live in comm.cuh -------
 extern "C" {
 
 // n x { inlet density, buffer = dens, step() } -- the body of run()'s loop (simulation.cpp:63-71)
@@ -42,7 +23,11 @@ int fluid_call(fluid_handle* h, int op, int b, int field_id, int prev_id, float 
     if (needs_prev && (prev_id < 0 || prev_id >= FLUID_NFIELDS || prev_id == field_id))
         return fl_fail(h, FLUID_E_ARG, "fluid_call(op=%d): bad prev field %d", op, prev_id);
     switch (op) {
-        case FLUID_OP_SET_BOUNDS:  return fl_set_bounds(h, b, field_id);
+        case FLUID_OP_SET_BOUNDS: {
+            if (int e = fl_set_bounds(h, b, field_id)) return e;
+            float* f[1] = { h->field[field_id] };
+            return fl_halo_exchange(h, 1, f);
+        }
         case FLUID_OP_LIN_SOLVE:   return fl_lin_solve(h, 1, &b, &field_id, &prev_id, a, c);
         case FLUID_OP_DIFFUSE:     return fl_diffuse(h, 1, &b, &field_id, &prev_id);
         case FLUID_OP_DIVERGENCE:  return fl_divergence(h);
@@ -55,6 +40,66 @@ int fluid_call(fluid_handle* h, int op, int b, int field_id, int prev_id, float 
         case FLUID_OP_COPY:        return fl_copy_field(h, field_id, prev_id);
     }
     return fl_fail(h, FLUID_E_ARG, "fluid_call: unknown op %d", op);
+}
+
+
+// ncclGetUniqueId for rank 0; the host program broadcasts the 128 bytes to the other ranks
+int fluid_comm_unique_id(const char* nccl_lib_path, char out[128])
+{
+    static SlabComm loader;
+    std::string err;
+    if (comm_load(&loader, nccl_lib_path, &err)) return fl_fail(nullptr, FLUID_E_COMM, "%s", err.c_str());
+    ncclUniqueId id;
+    ncclResult_t r = loader.GetUniqueId(&id);
+    if (r != ncclSuccess) return fl_fail(nullptr, FLUID_E_COMM, "ncclGetUniqueId: %s", loader.GetErrorString(r));
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    memcpy(out, &id, 128);
+    return 0;
+}
+
+int fluid_comm_init(fluid_handle* h, const char* nccl_lib_path, const char id_bytes[128])
+{
+    if (!h || !id_bytes) return FLUID_E_ARG;
+    if (h->nranks == 1) return 0;
+    if (!h->comm) h->comm = new SlabComm();
+    SlabComm* c = (SlabComm*)h->comm;
+    std::string err;
+    if (comm_load(c, nccl_lib_path, &err)) return fl_fail(h, FLUID_E_COMM, "%s", err.c_str());
+    ncclUniqueId id; memcpy(&id, id_bytes, 128);
+    FL_NCCL(h, c, c->CommInitRank(&c->comm, h->nranks, id, h->rank));
+    FL_CUDA(h, cudaMalloc(&c->d_token, sizeof(float)));
+    FL_CUDA(h, cudaMemsetAsync(c->d_token, 0, sizeof(float), h->stream));
+    return 0;
+}
+
+int fluid_ipc_export(fluid_handle* h, int field_id, char out[64])
+{
+    if (int e = check_field(h, field_id, "fluid_ipc_export")) return e;
+    cudaIpcMemHandle_t mh;
+    FL_CUDA(h, cudaIpcGetMemHandle(&mh, h->field[field_id] - h->g.plane));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");
+    memcpy(out, &mh, 64);
+    return 0;
+}
+
+int fluid_ipc_import(fluid_handle* h, int peer_rank, int field_id, const char in[64])
+{
+    if (int e = check_field(h, field_id, "fluid_ipc_import")) return e;
+    if (peer_rank < 0 || peer_rank >= h->nranks || peer_rank == h->rank)
+        return fl_fail(h, FLUID_E_ARG, "fluid_ipc_import: bad peer rank %d", peer_rank);
+    if (!h->comm) h->comm = new SlabComm();
+    SlabComm* c = (SlabComm*)h->comm;
+    cudaIpcMemHandle_t mh; memcpy(&mh, in, 64);
+    void* p = nullptr;
+    FL_CUDA(h, cudaIpcOpenMemHandle(&p, mh, cudaIpcMemLazyEnablePeerAccess));
+    c->peer_alloc[peer_rank][field_id] = (float*)p;
+    return 0;
+}
+
+int fluid_barrier(fluid_handle* h)
+{
+    if (!h) return FLUID_E_ARG;
+    return fl_barrier(h);
 }
 
 }  // extern "C"

@@ -7,6 +7,9 @@
 // multiple of 16 B (the TMA requirement).  The reference layout (x + y*(W+2) + z*(W+2)*(H+2),
 // simulation.h:9) only exists in the pack/unpack kernels at the host boundary.
 // zl is the LOCAL plane index of a z-slab: global z = zlo + zl - 1 (zlo = 1, Dl = D on one GPU).
+// Every volume is allocated with planes zl = -1 .. Dl+2 (the field pointer addresses plane 0): a slab
+// keeps TWO halo planes per interior side, because one fused red-black sweep needs the colour-0 update
+// of the neighbour's boundary plane, which is recomputed locally from the second halo plane.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -29,7 +32,8 @@ struct Grid {
     int pitch;            // floats per x-row
     int rows;             // H + 2
     long long plane;      // pitch * rows
-    long long cells;      // plane * (Dl + 2)   (allocated floats per field)
+    long long cells;      // plane * (Dl + 4)   (allocated floats per field, planes -1 .. Dl+2)
+    int zl_lo, zl_hi;     // local planes that hold real data: 0 / Dl+1 at the tunnel ends, -1 / Dl+2 inside
     int nxq;              // ceil(W / 4) x-quads per row
 };
 

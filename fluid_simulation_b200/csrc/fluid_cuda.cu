@@ -5,19 +5,22 @@
 #include "solver.cuh"
 #include "sweep_stream.cuh"
 #include "wavefront.cuh"
+#include "comm.cuh"
 #include <cstring>
 #include <new>
 
 thread_local std::string g_fluid_create_error;
 
-static Grid make_grid(int w, int h, int d, int zlo, int dl)
+static Grid make_grid(int w, int h, int d, int zlo, int dl, int rank, int nranks)
 {
     Grid g;
     g.W = w; g.H = h; g.D = d; g.Dl = dl; g.zlo = zlo;
     g.pitch = (w + 2 + FL_XOFF + 3) / 4 * 4;
     g.rows = h + 2;
     g.plane = (long long)g.pitch * g.rows;
-    g.cells = g.plane * (dl + 2);
+    g.cells = g.plane * (dl + 4);
+    g.zl_lo = rank == 0 ? 0 : -1;
+    g.zl_hi = rank == nranks - 1 ? dl + 1 : dl + 2;
     g.nxq = (w + 3) / 4;
     return g;
 }
@@ -29,17 +32,21 @@ static int alloc_all(fluid_handle* h)
     const size_t fbytes = (size_t)h->g.cells * sizeof(float);
     // one zeroed guard row in front of and behind every field keeps the float4 / scalar
     // neighbour loads of ghost-adjacent quads inside the allocation
+    // the handle's pointers address local plane 0; plane -1 precedes them (fl_base gives the allocation)
     for (int i = 0; i < FLUID_NFIELDS; ++i) {
         FL_CUDA(h, cudaMalloc(&h->field[i], fbytes));
         FL_CUDA(h, cudaMemsetAsync(h->field[i], 0, fbytes, h->stream));   // simulation.cpp:38-43
+        h->field[i] += h->g.plane;
     }
     for (int i = 0; i < 3; ++i) {
         FL_CUDA(h, cudaMalloc(&h->scratch[i], fbytes));
         FL_CUDA(h, cudaMemsetAsync(h->scratch[i], 0, fbytes, h->stream));
+        h->scratch[i] += h->g.plane;
     }
     FL_CUDA(h, cudaMalloc(&h->cflags, (size_t)h->g.cells));
     FL_CUDA(h, cudaMemsetAsync(h->cflags, 0, (size_t)h->g.cells, h->stream));
-    FL_CUDA(h, cudaMalloc(&h->staging, ref_plane_floats(h->g) * (h->g.Dl + 2) * sizeof(float)));
+    h->cflags += h->g.plane;
+    FL_CUDA(h, cudaMalloc(&h->staging, ref_plane_floats(h->g) * (h->g.Dl + 4) * sizeof(float)));
     h->n_partial = 148 * 8;
     FL_CUDA(h, cudaMalloc(&h->d_partial, (size_t)h->n_partial * FL_NSTAT * sizeof(double)));
     FL_CUDA(h, cudaMalloc(&h->d_out, FL_NSTAT * sizeof(double)));
@@ -50,7 +57,7 @@ static fluid_handle* create_impl(int w, int hgt, int d, int speed, float dt, flo
                                  int acc, unsigned flags, int rank, int nranks)
 {
     if (w < 1 || hgt < 1 || d < 1 || acc < 0 || nranks < 1 || rank < 0 || rank >= nranks || nranks > 8 ||
-        d < nranks) {
+        (nranks > 1 && d < 2 * nranks)) {
         fl_fail(nullptr, FLUID_E_ARG, "fluid_create: bad arguments (w=%d h=%d d=%d acc=%d rank=%d/%d)",
                 w, hgt, d, acc, rank, nranks);
         return nullptr;
@@ -91,7 +98,7 @@ static fluid_handle* create_impl(int w, int hgt, int d, int speed, float dt, flo
     int base = d / nranks, rem = d % nranks;
     int dl = base + (rank < rem ? 1 : 0);
     int zlo = 1 + rank * base + (rank < rem ? rank : rem);
-    h->g = make_grid(w, hgt, d, zlo, dl);
+    h->g = make_grid(w, hgt, d, zlo, dl, rank, nranks);
     h->speed = speed; h->dt = dt; h->diff = diff; h->visc = visc; h->acc = acc; h->flags = flags;
     h->rank = rank; h->nranks = nranks;
     bool ok = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess &&
@@ -138,10 +145,11 @@ void fluid_destroy(fluid_handle* h)
     if (h->dump_stream) cudaStreamSynchronize(h->dump_stream);
     fl_tiled_release(h);
     fl_comm_release(h);
-    for (int i = 0; i < FLUID_NFIELDS; ++i) cudaFree(h->field[i]);
-    for (int i = 0; i < 3; ++i) cudaFree(h->scratch[i]);
+    for (int i = 0; i < FLUID_NFIELDS; ++i) if (h->field[i]) cudaFree(h->field[i] - h->g.plane);
+    for (int i = 0; i < 3; ++i) if (h->scratch[i]) cudaFree(h->scratch[i] - h->g.plane);
     for (int i = 0; i < 5; ++i) cudaFree(h->frame_staging[i]);
-    cudaFree(h->cflags); cudaFree(h->staging); cudaFree(h->d_partial); cudaFree(h->d_out);
+    if (h->cflags) cudaFree(h->cflags - h->g.plane);
+    cudaFree(h->staging); cudaFree(h->d_partial); cudaFree(h->d_out);
     cudaFree(h->d_xyz); cudaFree(h->d_val);
     for (auto& r : h->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto e : h->ev_pool) cudaEventDestroy(e);

@@ -3,32 +3,34 @@
 #include "common.cuh"
 
 // ---- reference layout <-> pitched HBM layout (host boundary only) ----------------------------
-// host volume is the GLOBAL padded array; a slab moves local planes zl=0..Dl+1 <-> global z = zlo-1+zl.
-// `staging` holds exactly those planes in reference row order: (Dl+2) * (H+2) * (W+2) floats.
-__global__ void k_unpack(Grid g, const float* __restrict__ staging, float* __restrict__ field)
+// host volume is the GLOBAL padded array; a slab moves local planes zl <-> global z = zlo-1+zl.
+// `staging` holds `nplanes` planes starting at local plane zl_first in reference row order.
+__global__ void k_unpack(Grid g, int zl_first, int nplanes, const float* __restrict__ staging,
+                         float* __restrict__ field)
 {
     const int Wp = g.W + 2;
-    long long n = (long long)Wp * g.rows * (g.Dl + 2);
+    long long n = (long long)Wp * g.rows * nplanes;
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n;
          t += (long long)gridDim.x * blockDim.x) {
         int x = (int)(t % Wp);
         long long r = t / Wp;
         int y = (int)(r % g.rows);
-        int zl = (int)(r / g.rows);
+        int zl = zl_first + (int)(r / g.rows);
         field[fl_idx(g, x, y, zl)] = staging[t];
     }
 }
 
-__global__ void k_pack(Grid g, const float* __restrict__ field, float* __restrict__ staging)
+__global__ void k_pack(Grid g, int zl_first, int nplanes, const float* __restrict__ field,
+                       float* __restrict__ staging)
 {
     const int Wp = g.W + 2;
-    long long n = (long long)Wp * g.rows * (g.Dl + 2);
+    long long n = (long long)Wp * g.rows * nplanes;
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n;
          t += (long long)gridDim.x * blockDim.x) {
         int x = (int)(t % Wp);
         long long r = t / Wp;
         int y = (int)(r % g.rows);
-        int zl = (int)(r / g.rows);
+        int zl = zl_first + (int)(r / g.rows);
         staging[t] = field[fl_idx(g, x, y, zl)];
     }
 }
@@ -37,13 +39,14 @@ __global__ void k_pack(Grid g, const float* __restrict__ field, float* __restric
 // Encodes exactly the obs tests the reference performs: `== 1.0f` for solid, `== 0.0f` plus the
 // 1..dim range test for "open" neighbours (simulation.cpp:222, 232-238, 307-312, 329-355).
 // obs has valid halo planes in slab mode, so the +-z tests see the neighbouring slab's mask.
+// obs / flags are the ALLOCATION bases (plane -1 first); index t runs over the whole allocation.
 __global__ void k_build_flags(Grid g, const float* __restrict__ obs, unsigned char* __restrict__ flags)
 {
     long long n = g.cells;
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n;
          t += (long long)gridDim.x * blockDim.x) {
         long long r = t;
-        int zl = (int)(r / g.plane); r -= (long long)zl * g.plane;
+        int zl = (int)(r / g.plane); r -= (long long)zl * g.plane; zl -= 1;
         int y = (int)(r / g.pitch);
         int x = (int)(r - (long long)y * g.pitch) - FL_XOFF;
         int gz = g.zlo + zl - 1;
@@ -75,8 +78,9 @@ __global__ void k_build_flags(Grid g, const float* __restrict__ obs, unsigned ch
 __global__ void k_inflow_density(Grid g, float* __restrict__ dens, float amount)
 {
     int y = 1 + blockIdx.x * blockDim.x + threadIdx.x;
-    int zl = 1 + blockIdx.y;
-    if (y <= g.H) dens[fl_idx(g, 1, y, zl)] += amount;
+    int zl = (int)blockIdx.y - 1;                // -1 .. Dl+2: a slab also keeps its two halo planes current
+    int gz = g.zlo + zl - 1;
+    if (y <= g.H && gz >= 1 && gz <= g.D) dens[fl_idx(g, 1, y, zl)] += amount;
 }
 
 // step(): v(1,j,k) = (speed, 0, 0)        simulation.cpp:103-105
@@ -84,8 +88,9 @@ __global__ void k_inflow_velocity(Grid g, float* __restrict__ vx, float* __restr
                                   float* __restrict__ vz, float speed)
 {
     int y = 1 + blockIdx.x * blockDim.x + threadIdx.x;
-    int zl = 1 + blockIdx.y;
-    if (y <= g.H) {
+    int zl = (int)blockIdx.y - 1;
+    int gz = g.zlo + zl - 1;
+    if (y <= g.H && gz >= 1 && gz <= g.D) {
         long long c = fl_idx(g, 1, y, zl);
         vx[c] = speed; vy[c] = 0.0f; vz[c] = 0.0f;
     }
@@ -132,7 +137,7 @@ __global__ void k_add_density(Grid g, float* __restrict__ dens, int n, const int
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     int zl = xyz[3 * t + 2] - g.zlo + 1;
-    if (zl < 0 || zl > g.Dl + 1) return;
+    if (zl < g.zl_lo || zl > g.zl_hi) return;
     atomicAdd(&dens[fl_idx(g, xyz[3 * t], xyz[3 * t + 1], zl)], amount[t]);
 }
 
@@ -143,7 +148,7 @@ __global__ void k_set_velocity(Grid g, float* __restrict__ vx, float* __restrict
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     int zl = xyz[3 * t + 2] - g.zlo + 1;
-    if (zl < 0 || zl > g.Dl + 1) return;
+    if (zl < g.zl_lo || zl > g.zl_hi) return;
     long long c = fl_idx(g, xyz[3 * t], xyz[3 * t + 1], zl);
     vx[c] = v[3 * t]; vy[c] = v[3 * t + 1]; vz[c] = v[3 * t + 2];
 }
@@ -153,6 +158,6 @@ __global__ void k_add_obstacles(Grid g, float* __restrict__ obs, int n, const in
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     int zl = xyz[3 * t + 2] - g.zlo + 1;
-    if (zl < 0 || zl > g.Dl + 1) return;
+    if (zl < g.zl_lo || zl > g.zl_hi) return;
     obs[fl_idx(g, xyz[3 * t], xyz[3 * t + 1], zl)] = 1.0f;
 }

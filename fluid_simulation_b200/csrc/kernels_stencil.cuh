@@ -58,11 +58,14 @@ __global__ void __launch_bounds__(256) k_sweep_jacobi(Grid g, SweepBatch sb,
 // ---- red-black half sweep, in place, no bounds (they run after the black half) ---------------
 // colour 0 = cells with (i+j+l) even, global coordinates.  Only cells of `colour` change; the
 // other two lanes of the quad are written back unchanged (nobody else writes them in this pass).
+// Planes zl_first .. zl_first+nplanes-1 are swept: 1..Dl normally; a z-slab runs colour 0 also on its
+// first halo plane (0 / Dl+1 where that plane is interior to the tunnel) so that the colour-1 pass sees
+// the neighbour's colour-0 update without an exchange in the middle of the sweep.
 __global__ void __launch_bounds__(256) k_sweep_rb_half(Grid g, SweepBatch sb, float a, float c_recip,
-                                                       int colour)
+                                                       int colour, int zl_first, int nplanes)
 {
-    const int batch = blockIdx.z / g.Dl;
-    QuadPos p = fl_quad_pos(g, 1 + blockIdx.z % g.Dl);
+    const int batch = blockIdx.z / nplanes;
+    QuadPos p = fl_quad_pos(g, zl_first + blockIdx.z % nplanes);
     if (!p.valid) return;
     float* __restrict__ f = sb.dst[batch];
     const float* __restrict__ rhs = sb.rhs[batch];

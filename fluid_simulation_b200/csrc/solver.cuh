@@ -8,18 +8,20 @@
 #include "kernels_reduce.cuh"
 #include <math.h>
 
-int fl_halo_exchange(fluid_handle* h, int n, float* const* fields);      // fluid_cuda.cu (slab mode)
+int fl_halo_exchange(fluid_handle* h, int n, float* const* fields);      // comm.cuh (slab mode)
 int fl_lex_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
                  float a, float c);                                      // wavefront.cuh
 int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
                    float a, float c, bool* handled);                     // tiled.cuh
 void fl_tiled_release(fluid_handle* h);                                  // tiled.cuh
-void fl_comm_release(fluid_handle* h);                                   // api_ops.inl
+void fl_comm_release(fluid_handle* h);                                   // comm.cuh
+int fl_barrier(fluid_handle* h);                                         // comm.cuh
 
 static inline int fl_rebuild_flags(fluid_handle* h)
 {
     if (!h->flags_dirty) return 0;
-    k_build_flags<<<fl_grid_1d(h->g.cells), 256, 0, h->stream>>>(h->g, h->field[FLUID_OBS], h->cflags);
+    k_build_flags<<<fl_grid_1d(h->g.cells), 256, 0, h->stream>>>(h->g, h->field[FLUID_OBS] - h->g.plane,
+                                                                 h->cflags - h->g.plane);
     FL_CHECK_LAUNCH(h);
     h->flags_dirty = false;
     return 0;
@@ -110,7 +112,11 @@ static inline int fl_lin_solve_impl(fluid_handle* h, int nb, const int* b, const
         } else {  // red-black, in place: colour 0, colour 1, then setBounds
             for (int i = 0; i < nb; ++i) { sb.src[i] = cur[i]; sb.dst[i] = cur[i]; }
             for (int colour = 0; colour < 2; ++colour) {
-                k_sweep_rb_half<<<q.grid, q.block, 0, h->stream>>>(g, sb, a, c_recip, colour);
+                // colour 0 also covers a slab's first halo planes (see k_sweep_rb_half)
+                const int zf = (colour == 0 && h->rank > 0) ? 0 : 1;
+                const int zl = (colour == 0 && h->rank < h->nranks - 1) ? g.Dl + 1 : g.Dl;
+                QuadLaunch qh = fl_quad_launch(g, (zl - zf + 1) * nb);
+                k_sweep_rb_half<<<qh.grid, qh.block, 0, h->stream>>>(g, sb, a, c_recip, colour, zf, zl - zf + 1);
                 FL_CHECK_LAUNCH(h);
             }
             QuadLaunch qb = fl_quad_launch(g, g.Dl);
@@ -145,7 +151,10 @@ static inline int fl_divergence(fluid_handle* h)
                                                     h->field[FLUID_DIVERGENCE], h->field[FLUID_PRESSURE],
                                                     fl_project_h(h));
     FL_CHECK_LAUNCH(h);
-    if (h->nranks > 1) { float* f[1] = { h->field[FLUID_PRESSURE] }; if (int e = fl_halo_exchange(h, 1, f)) return e; }
+    if (h->nranks > 1) {   // the Poisson sweeps read both on the halo planes
+        float* f[2] = { h->field[FLUID_DIVERGENCE], h->field[FLUID_PRESSURE] };
+        if (int e = fl_halo_exchange(h, 2, f)) return e;
+    }
     return 0;
 }
 
@@ -157,6 +166,10 @@ static inline int fl_gradient(fluid_handle* h)
                                                   h->field[FLUID_VX], h->field[FLUID_VY],
                                                   h->field[FLUID_VZ], fl_project_h(h));
     FL_CHECK_LAUNCH(h);
+    if (h->nranks > 1) {
+        float* f[3] = { h->field[FLUID_VX], h->field[FLUID_VY], h->field[FLUID_VZ] };
+        if (int e = fl_halo_exchange(h, 3, f)) return e;
+    }
     return 0;
 }
 
@@ -175,17 +188,22 @@ static inline int fl_advect(fluid_handle* h, int b, int fid, int pid)     // sim
     if (int e = fl_rebuild_flags(h)) return e;
     GatherSrc src;
     if (int e = fl_gather_sources(h, pid, &src)) return e;
+    if (int e = fl_barrier(h)) return e;          // every rank's slab of the gather source is complete
     QuadLaunch q = fl_quad_launch(h->g, h->g.Dl);
     k_advect<<<q.grid, q.block, 0, h->stream>>>(h->g, b, h->field[fid], h->field[pid], src,
                                                 h->field[FLUID_VX], h->field[FLUID_VY],
                                                 h->field[FLUID_VZ], h->cflags, h->dt);
     FL_CHECK_LAUNCH(h);
+    if (h->nranks > 1) {
+        float* f[1] = { h->field[fid] };
+        if (int e = fl_halo_exchange(h, 1, f)) return e;
+    }
     return 0;
 }
 
 static inline int fl_inflow_density(fluid_handle* h)                      // simulation.cpp:65-67
 {
-    dim3 grid((h->g.H + 127) / 128, h->g.Dl);
+    dim3 grid((h->g.H + 127) / 128, h->g.Dl + 4);
     k_inflow_density<<<grid, 128, 0, h->stream>>>(h->g, h->field[FLUID_DENS], 0.001f);
     FL_CHECK_LAUNCH(h);
     return 0;
@@ -193,7 +211,7 @@ static inline int fl_inflow_density(fluid_handle* h)                      // sim
 
 static inline int fl_inflow_velocity(fluid_handle* h)                     // simulation.cpp:103-105
 {
-    dim3 grid((h->g.H + 127) / 128, h->g.Dl);
+    dim3 grid((h->g.H + 127) / 128, h->g.Dl + 4);
     k_inflow_velocity<<<grid, 128, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY],
                                                    h->field[FLUID_VZ], (float)h->speed);
     FL_CHECK_LAUNCH(h);
@@ -202,7 +220,7 @@ static inline int fl_inflow_velocity(fluid_handle* h)                     // sim
 
 static inline int fl_copy_field(fluid_handle* h, int dst, int src)
 {
-    FL_CUDA(h, cudaMemcpyAsync(h->field[dst], h->field[src], (size_t)h->g.cells * sizeof(float),
+    FL_CUDA(h, cudaMemcpyAsync(h->field[dst] - h->g.plane, h->field[src] - h->g.plane, (size_t)h->g.cells * sizeof(float),
                                cudaMemcpyDeviceToDevice, h->stream));
     return 0;
 }
@@ -228,7 +246,8 @@ static inline int fl_step_only(fluid_handle* h)
         const int b = 0, f = FLUID_DENS, p = FLUID_BUFFER;
         if (int e = fl_diffuse(h, 1, &b, &f, &p)) return e;
     }
-    return fl_advect(h, 0, FLUID_DENS, FLUID_BUFFER);                     // :136
+    if (int e = fl_advect(h, 0, FLUID_DENS, FLUID_BUFFER)) return e;      // :136
+    return fl_barrier(h);        // slab mode: nobody overwrites a gather source while a peer still reads it
 }
 
 // one iteration of run()'s loop body (simulation.cpp:65-71)

@@ -248,7 +248,9 @@ __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float*
     const float4& mA = t.QA[IM]; const float4& mB = t.QB[IM];
     const float* Vq = vbuf + ((U + 1) & 1) * XSLOTF;                 // published (and synced) last step
     const int q = p - DIR;
-    const bool do0 = MODE == 1 && p >= 1 && p <= g.Dl && !(A.dbg & 2), do1 = MODE == 1 && q >= za && q <= zb && !(A.dbg & 2);
+    // stage 0 runs on every plane that is interior to the TUNNEL: on a z-slab that includes the first
+    // halo plane, whose colour-0 update is recomputed locally from the second halo plane
+    const bool do0 = MODE == 1 && (unsigned)(g.zlo + p - 2) < (unsigned)g.D && !(A.dbg & 2), do1 = MODE == 1 && q >= za && q <= zb && !(A.dbg & 2);
     float4 ymA0 = cA, ypB0 = cB, ymA1 = cA, ypB1 = cB;
     float L0 = 0.0f, R0 = 0.0f, L1 = 0.0f, R1 = 0.0f;
     if (do0) {
@@ -380,7 +382,7 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
         const int batch = sg.col / A.nty;
         const int y0 = 1 + (sg.col - batch * A.nty) * GE::TY;        // first owned row (odd)
         const int za = sg.za, zb = sg.zb;
-        const int lo = max(za - 2, 0), hi = min(zb + 2, g.Dl + 1);   // planes this segment reads
+        const int lo = max(za - 2, g.zl_lo), hi = min(zb + 2, g.zl_hi);   // planes this segment reads
         const int ps = DIR > 0 ? za - 1 : zb + 1;                    // first stage-0 plane
         const int nsteps = zb - za + 3;
         const bool has_behind = DIR > 0 ? (ps - 1 >= lo) : (ps + 1 <= hi);
@@ -396,8 +398,9 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
             float* slot = uring + s_iss * SLOTF;
 #pragma unroll
             for (int i = 0; i < TXW; ++i) {
-                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p, bar);
-                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p, bar);
+                // the tensor maps start at the allocation's plane -1, hence p + 1
+                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p + 1, bar);
+                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p + 1, bar);
             }
             if (++s_iss == NSLOT) s_iss = 0;
             // ... and the plane SW_L2_AHEAD steps further on starts its way from HBM into L2
@@ -405,8 +408,8 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
             if (A.l2_ahead > 0 && pf >= lo && pf <= hi) {
 #pragma unroll
                 for (int i = 0; i < TXW; ++i) {
-                    sw_tma_prefetch_3d(&A.map[batch], 128 * i, y0 - 2, pf);
-                    sw_tma_prefetch_3d(&A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, pf);
+                    sw_tma_prefetch_3d(&A.map[batch], 128 * i, y0 - 2, pf + 1);
+                    sw_tma_prefetch_3d(&A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, pf + 1);
                 }
             }
         };
@@ -528,11 +531,11 @@ inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows
     if (it == s->maps.end()) {
         const Grid& g = h->g;
         CUtensorMap m;
-        cuuint64_t dims[3] = { (cuuint64_t)g.pitch, (cuuint64_t)g.rows, (cuuint64_t)(g.Dl + 2) };
+        cuuint64_t dims[3] = { (cuuint64_t)g.pitch, (cuuint64_t)g.rows, (cuuint64_t)(g.Dl + 4) };   // planes -1 .. Dl+2
         cuuint64_t strides[2] = { (cuuint64_t)g.pitch * 4, (cuuint64_t)g.plane * 4 };
         cuuint32_t box[3] = { (cuuint32_t)box_w, (cuuint32_t)box_rows, 1 };
         cuuint32_t estr[3] = { 1, 1, 1 };
-        CUresult r = s->encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)buf, dims, strides, box, estr,
+        CUresult r = s->encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)(buf - g.plane), dims, strides, box, estr,
                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return fl_fail(h, FLUID_E_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
@@ -668,6 +671,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         kern<<<plan.nctas, GE::THREADS, GE::SMEM, h->stream>>>(A);
         FL_CHECK_LAUNCH(h);
         for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
+        if (h->nranks > 1) if (int e = fl_halo_exchange(h, nb, cur)) return e;     // two planes each way
     }
     if (pin) {
         cudaStreamAttrValue av = {};
@@ -687,7 +691,6 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
     const Grid& g = h->g;
     const unsigned solver = h->flags & FLUID_SOLVER_MASK;
     if (solver != FLUID_SOLVER_RB && solver != FLUID_SOLVER_JACOBI) return 0;
-    if (h->nranks > 1) return 0;                         // slab mode exchanges halos per half sweep (simple path)
     if ((g.W & 3) || g.W > 512) return 0;                // quads must not straddle the x = W+1 ghost
     if (!(h->flags & FLUID_TILED_ALWAYS) && (g.W < 64 || g.H < 8 || g.Dl < 4)) return 0;
     StreamState* s = sw_state(h);

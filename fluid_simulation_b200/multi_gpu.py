@@ -1,0 +1,86 @@
+"""Attach a z-slab `Simulation` (one process per GPU) to its peers.
+
+The solver library owns the data path: halo planes move by ncclSend/ncclRecv inside libfluid_cuda
+(its own communicator) and advection gathers read the peers' slabs through CUDA IPC mappings.  This
+module only does the rendezvous that needs a process group -- `torch.distributed` is plumbing here:
+broadcast of the 128-byte NCCL unique id and all-gather of the 64-byte IPC handles.  It works with any
+backend (`nccl` on the GPU box; the `gloo` tests exercise the same code with a fake library).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from .simulation import FIELDS, FluidError
+
+# the fields advect() gathers from: prev_field of each of the four calls (simulation.cpp:125-127, 136)
+GATHER_SOURCES = ("v_x_prev", "v_y_prev", "v_z_prev", "buffer")
+
+
+def nccl_library_path() -> str:
+    """The libnccl the host process already uses (torch's bundled wheel), else the system one."""
+    try:
+        import nvidia.nccl as n
+        p = os.path.join(os.path.dirname(n.__file__), "lib", "libnccl.so.2")
+        if os.path.exists(p):
+            return p
+    except Exception:
+        pass
+    return "libnccl.so.2"
+
+
+def broadcast_bytes(dist, payload: bytes | None, n: int, src: int = 0) -> bytes:
+    """Every rank gets rank `src`'s `n` bytes."""
+    box = [payload if dist.get_rank() == src else None]
+    dist.broadcast_object_list(box, src=src)
+    out = bytes(box[0])
+    if len(out) != n:
+        raise FluidError(f"broadcast_bytes: expected {n} bytes, got {len(out)}")
+    return out
+
+
+def all_gather_bytes(dist, payload):
+    """List over ranks of each rank's (picklable) payload."""
+    out = [None] * dist.get_world_size()
+    dist.all_gather_object(out, payload)
+    return out
+
+
+def attach(sim, dist, lib=None) -> None:
+    """Collective over `dist`'s default group: give the slab handle its NCCL communicator and map the
+    peers' gather sources.  `lib` defaults to the loaded libfluid_cuda (a stand-in is injected by tests)."""
+    L = lib if lib is not None else sim._L
+    rank, world = dist.get_rank(), dist.get_world_size()
+    if world != sim.nranks or rank != sim.rank:
+        raise FluidError(f"process group ({rank}/{world}) does not match the slab handle ({sim.rank}/{sim.nranks})")
+    if world == 1:
+        return
+    path = nccl_library_path().encode()
+    uid = None
+    if rank == 0:
+        buf = C.create_string_buffer(128)
+        sim._ck(L.fluid_comm_unique_id(path, buf))
+        uid = buf.raw
+    uid = broadcast_bytes(dist, uid, 128)
+    sim._ck(L.fluid_comm_init(sim._h, path, uid))
+    mine = {}
+    for name in GATHER_SOURCES:
+        buf = C.create_string_buffer(64)
+        sim._ck(L.fluid_ipc_export(sim._h, FIELDS[name], buf))
+        mine[name] = buf.raw
+    for r, handles in enumerate(all_gather_bytes(dist, mine)):
+        if r == rank:
+            continue
+        for name in GATHER_SOURCES:
+            sim._ck(L.fluid_ipc_import(sim._h, r, FIELDS[name], handles[name]))
+    dist.barrier()
+
+
+def reduce_stats(dist, st: dict) -> dict:
+    """Combine per-slab run() statistics (simulation.cpp:73-90): sums add, minima / maxima fold."""
+    parts = all_gather_bytes(dist, st)
+    out = {}
+    for k in st:
+        vals = [p[k] for p in parts]
+        out[k] = sum(vals) if k.endswith("_sum") else (min(vals) if k.endswith("_min") else max(vals))
+    return out

@@ -16,14 +16,17 @@ def partition(depth: int, nranks: int):
 
 
 def halo_plan(depth: int, nranks: int, rank: int):
-    """Neighbour ranks and the LOCAL plane indices exchanged per halo update:
-    send local plane 1 down / receive into local plane 0, send plane d_local up / receive into
-    plane d_local+1.  Global ghost planes (z=0, z=D+1) belong to the end slabs and are not exchanged."""
+    """Neighbour ranks and the LOCAL plane indices exchanged per halo update (two planes per side: one
+    fused red-black sweep recomputes the colour-0 update of the neighbour's boundary plane from the second
+    halo plane): send local planes 1,2 down / receive into planes -1,0; send planes d_local-1,d_local up /
+    receive into d_local+1,d_local+2.  Global ghost planes (z=0, z=D+1) belong to the end slabs and are not
+    exchanged.  The same rule is implemented by libfluid_cuda's fl_halo_exchange (csrc/comm.cuh)."""
     z_lo, dl = partition(depth, nranks)[rank]
     return {
         "z_lo": z_lo, "d_local": dl,
-        "down": None if rank == 0 else {"peer": rank - 1, "send_plane": 1, "recv_plane": 0},
-        "up": None if rank == nranks - 1 else {"peer": rank + 1, "send_plane": dl, "recv_plane": dl + 1},
+        "down": None if rank == 0 else {"peer": rank - 1, "send_planes": (1, 2), "recv_planes": (-1, 0)},
+        "up": None if rank == nranks - 1 else {"peer": rank + 1, "send_planes": (dl - 1, dl),
+                                               "recv_planes": (dl + 1, dl + 2)},
     }
 
 

@@ -77,8 +77,10 @@ fluid_handle* fluid_create(int w, int h, int d, int speed, float dt, float diff,
                            int acc, unsigned flags);
 
 /* z-slab member of a multi-GPU run: this process owns global planes z_lo..z_lo+d_local-1 of a
- * w x h x d tunnel.  `rank`/`nranks` order the slabs along z.  Halo planes are
- * exchanged through the callbacks registered with fluid_set_exchange (NCCL in bench.py). */
+ * w x h x d tunnel (the reference has no distributed mode).  `rank`/`nranks` order the
+ * slabs along z (equal slabs, remainder planes to the low ranks; d >= 2*nranks).  Before the first
+ * device operation the host program attaches the communicator (fluid_comm_init) and maps the peers'
+ * advection sources (fluid_ipc_export / fluid_ipc_import); see fluid_simulation_b200/multi_gpu.py. */
 fluid_handle* fluid_create_slab(int w, int h, int d, int speed, float dt, float diff, float visc,
                                 int acc, unsigned flags, int rank, int nranks);
 
@@ -150,6 +152,21 @@ const char* fluid_version(void);
 
 /* select the CUDA device subsequent fluid_create calls of this thread use (cudaSetDevice) */
 int fluid_set_device(int device);
+
+/* ---- multi-GPU z-slabs: one process per GPU on one NVLink/NVSwitch box ------------------------
+ * Halo planes (two per interior side) travel by ncclSend/ncclRecv on the solver stream after every
+ * sweep and around divergence / gradient / advect; libnccl is dlopen'ed from `nccl_lib_path` (NULL or
+ * "" = the process's libnccl.so.2).  Rank 0 calls fluid_comm_unique_id and the host program hands the
+ * 128 bytes to every rank (e.g. torch.distributed broadcast); fluid_comm_init is collective. */
+int fluid_comm_unique_id(const char* nccl_lib_path, char out[128]);
+int fluid_comm_init(fluid_handle*, const char* nccl_lib_path, const char unique_id[128]);
+/* advect() gathers at arbitrary z (simulation.cpp:384-397): the gather sources v_x_prev, v_y_prev,
+ * v_z_prev and buffer of every other rank are mapped through CUDA IPC (64-byte handles, exchanged by
+ * the host program) and read over NVLink by the advection kernel. */
+int fluid_ipc_export(fluid_handle*, int field_id, char out[64]);
+int fluid_ipc_import(fluid_handle*, int peer_rank, int field_id, const char in[64]);
+/* device-side barrier across all ranks on the handle's stream (collective) */
+int fluid_barrier(fluid_handle*);
 
 #ifdef __cplusplus
 }
