@@ -1,0 +1,80 @@
+// fluid_tunnel -- parametrised replacement of the reference's hard-coded main() (simulation.cpp:429-450):
+// builds a Simulation, installs an obstacle mask, runs `iter` steps, writes data/*.bin frames in the
+// reference's format and prints run()'s statistics plus the device time per step.
+//   fluid_tunnel [--w 128 --h 64 --d 64 --iter 100 --acc 15 --speed 30] [--obstacle none|sphere|box|FILE.bin]
+//                [--solver rb|jacobi|lex] [--elide] [--out data] [--dump-every 1] [--quiet]
+// FILE.bin = raw float32 padded mask (w+2)(h+2)(d+2) in the reference layout, e.g. dumped once from the
+// reference's STL loader (its output is not reproducible run to run).
+#include "simulation.h"
+#include "../../include/fluid_cuda.h"
+
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <stdexcept>
+
+static std::vector<float> analytic_mask(const std::string& kind, int w, int h, int d)
+{
+    std::vector<float> m((size_t)(w + 2) * (h + 2) * (d + 2), 0.0f);
+    auto at = [&](int x, int y, int z) -> float& { return m[(size_t)x + (size_t)y * (w + 2) + (size_t)z * (w + 2) * (h + 2)]; };
+    for (int z = 1; z <= d; ++z)
+        for (int y = 1; y <= h; ++y)
+            for (int x = 1; x <= w; ++x) {
+                bool in = false;
+                if (kind == "sphere") {          // dist to (0.35W, 0.5H, 0.5D) <= 0.15H, float32
+                    const float cx = (float)(0.35 * w), cy = (float)(0.5 * h), cz = (float)(0.5 * d), r = (float)(0.15 * h);
+                    const float dx = (float)x - cx, dy = (float)y - cy, dz = (float)z - cz;
+                    in = dx * dx + dy * dy + dz * dz <= r * r;
+                } else if (kind == "box") {
+                    in = x >= 0.3 * w && x <= 0.45 * w && y >= 0.35 * h && y <= 0.65 * h && z >= 0.35 * d && z <= 0.65 * d;
+                }
+                if (in) at(x, y, z) = 1.0f;
+            }
+    return m;
+}
+
+int main(int argc, char** argv)
+{
+    int w = 128, h = 64, d = 64, iter = 100, acc = 15, speed = 30, dump_every = 1;   // simulation.cpp:431-436
+    std::string obstacle = "none", solver = "rb", out = "data";
+    bool elide = false, quiet = false;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        auto val = [&]() -> const char* { if (i + 1 >= argc) { std::cerr << a << " needs a value\n"; std::exit(2); } return argv[++i]; };
+        if (a == "--w") w = std::atoi(val()); else if (a == "--h") h = std::atoi(val());
+        else if (a == "--d") d = std::atoi(val()); else if (a == "--iter") iter = std::atoi(val());
+        else if (a == "--acc") acc = std::atoi(val()); else if (a == "--speed") speed = std::atoi(val());
+        else if (a == "--obstacle") obstacle = val(); else if (a == "--solver") solver = val();
+        else if (a == "--out") out = val(); else if (a == "--dump-every") dump_every = std::atoi(val());
+        else if (a == "--elide") elide = true; else if (a == "--quiet") quiet = true;
+        else { std::cerr << "unknown argument " << a << "\n"; return 2; }
+    }
+    unsigned flags = solver == "jacobi" ? FLUID_SOLVER_JACOBI : solver == "lex" ? FLUID_SOLVER_LEX : FLUID_SOLVER_RB;
+    if (elide) flags |= FLUID_ELIDE_DEAD;
+    try {
+        Simulation sim(w, h, d, iter, speed, 0.05f, 2.0e-5f, 1.5e-5f, acc, flags);
+        sim.quiet = quiet; sim.dump_every = dump_every > 0 ? dump_every : 1;
+        sim.setOutputDirectory(out);
+        if (obstacle == "sphere" || obstacle == "box") {
+            std::vector<float> m = analytic_mask(obstacle, w, h, d);
+            sim.uploadObstacles(m.data());
+        } else if (obstacle != "none") {
+            std::vector<float> m((size_t)(w + 2) * (h + 2) * (d + 2));
+            std::ifstream f(obstacle, std::ios::binary);
+            if (!f.read((char*)m.data(), (std::streamsize)(m.size() * sizeof(float))))
+                throw std::runtime_error("cannot read obstacle mask " + obstacle);
+            sim.uploadObstacles(m.data());
+        }
+        sim.run();
+        if (!quiet) {
+            const double cells = (double)w * h * d;
+            std::cout << fluid_version() << "\n" << sim.msPerStepLastRun() << " ms per step (incl. frame dumps), "
+                      << cells / (sim.msPerStepLastRun() * 1e-3) / 1e9 << " G cell-updates/s\n";
+        }
+    } catch (const std::exception& e) {
+        std::cerr << "fluid_tunnel: " << e.what() << "\n";
+        return 1;
+    }
+    return 0;
+}

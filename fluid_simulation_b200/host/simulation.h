@@ -1,0 +1,76 @@
+// simulation.h -- the reference's `Simulation` class (/root/reference/simulation.h:11-91) over
+// libfluid_cuda: same public data members, constructor and methods; the eleven std::vector<float>
+// fields and the five private solver methods are replaced by a fluid_handle* (include/fluid_cuda.h).
+// All compute runs on the B200; there is no CPU path (the constructor throws if no device is usable).
+#ifndef FLUID_B200_SIMULATION_H
+#define FLUID_B200_SIMULATION_H
+
+#include <cstdio>
+#include <string>
+#include <vector>
+
+struct fluid_handle;
+
+class Simulation {
+private:
+    fluid_handle* h_ = nullptr;
+
+    // addObstacle / addDensity / setVelocity are per-cell calls (the STL loader makes millions,
+    // object_loader.cpp:439-442): they are staged here and flushed in order before the next device op
+    enum Kind { NONE, OBS, DENS, VEL };
+    Kind pending_ = NONE;
+    std::vector<int> xyz_;
+    std::vector<float> val_;
+    void stage(Kind k);
+    void flush();
+
+    // frame output (simulation.cpp:56-60, 140-148): pinned double buffer, written while the next step runs
+    std::string out_dir_ = "data";
+    std::FILE* files_[5] = {};
+    float* frame_[5] = {};
+    bool frame_pending_ = false;
+    void write_pending_frame();
+    void check(int rc, const char* what) const;
+
+public:
+    /* grid dimensions (without padding), inlet speed, parameters: simulation.h:44-54 */
+    int width, height, depth;
+    int speed;
+    float dt, diff, visc;
+    int acc, iter;
+
+    /* extras of the B200 build (defaults reproduce the reference): */
+    unsigned flags = 0;          // FLUID_SOLVER_RB (default) | FLUID_SOLVER_JACOBI | FLUID_SOLVER_LEX | FLUID_ELIDE_DEAD
+    int dump_every = 1;          // the reference writes a frame every step (simulation.cpp:140-148)
+    bool quiet = false;
+
+    Simulation(int w, int h, int d, int iter, int speed = 30, float dt = 0.05f, float diff = 2.0e-5f,
+               float visc = 1.5e-5f, int acc = 15, unsigned flags = 0);
+    ~Simulation();
+    Simulation(const Simulation&) = delete;
+    Simulation& operator=(const Simulation&) = delete;
+
+    void run();                                   // simulation.cpp:49-91
+    void step();                                  // simulation.cpp:96-150 (incl. the frame write)
+    void addObstacle(int x, int y, int z);        // simulation.cpp:155
+    void addDensity(int x, int y, int z, float amount);                       // :163
+    void setVelocity(int x, int y, int z, float ax, float ay, float az);      // :172
+
+    /* access that the reference gave through its (private) vectors */
+    void setOutputDirectory(const std::string& dir) { out_dir_ = dir; }
+    void uploadObstacles(const float* obs_padded);                            // whole mask at once
+    void downloadField(int field_id, float* padded_host);
+    void statistics(double out[9]);
+    double msPerStepLastRun() const { return ms_per_step_; }
+    fluid_handle* handle() { flush(); return h_; }
+
+private:
+    double ms_per_step_ = 0.0;
+};
+
+/* Load STL and populate obstacles: the reference's object_loader.cpp compiles unchanged against this
+ * header (it only uses width/height/depth and addObstacle). */
+void loadSTLIntoObstacles(const char* stlFile, Simulation& sim, float scale, float rot_x, float rot_y,
+                          float rot_z, float translate_x, float translate_y, float translate_z);
+
+#endif
