@@ -17,6 +17,8 @@ buffers: initial obstacle upload H2D, every step followed by the reference's fra
 from __future__ import annotations
 
 import argparse
+import contextlib
+import io
 import json
 import os
 import subprocess
@@ -307,9 +309,23 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3                                   # timing rule: W >= 3
-    if args.impl == "reference":
-        return run_reference_arm(args)
-    return run_ours(args)
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) are sent
+    # to stderr for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    out = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(out):
+            rc = run_reference_arm(args) if args.impl == "reference" else run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    lines = [l for l in out.getvalue().splitlines() if l.startswith("{")]
+    if lines:
+        print(lines[-1], flush=True)
+    return rc
 
 
 if __name__ == "__main__":

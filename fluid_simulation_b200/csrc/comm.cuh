@@ -57,7 +57,7 @@ static inline void fl_slab_of(int d, int nranks, int r, int* zlo, int* dl)
 }
 
 // Send my planes {1,2} down and {Dl-1,Dl} up, receive the neighbours' into {Dl+1,Dl+2} / {-1,0}.
-int fl_halo_exchange(fluid_handle* h, int n, float* const* fields)
+int fl_halo_exchange_on(fluid_handle* h, int n, float* const* fields, cudaStream_t stream)
 {
     if (h->nranks == 1) return 0;
     SlabComm* c = (SlabComm*)h->comm;
@@ -69,18 +69,20 @@ int fl_halo_exchange(fluid_handle* h, int n, float* const* fields)
     for (int i = 0; i < n; ++i) {
         float* f = fields[i];
         if (h->rank > 0) {
-            FL_NCCL(h, c, c->Send(f + 1 * pl, cnt, ncclFloat, h->rank - 1, c->comm, h->stream));
-            FL_NCCL(h, c, c->Recv(f - 1 * pl, cnt, ncclFloat, h->rank - 1, c->comm, h->stream));
+            FL_NCCL(h, c, c->Send(f + 1 * pl, cnt, ncclFloat, h->rank - 1, c->comm, stream));
+            FL_NCCL(h, c, c->Recv(f - 1 * pl, cnt, ncclFloat, h->rank - 1, c->comm, stream));
         }
         if (h->rank < h->nranks - 1) {
-            FL_NCCL(h, c, c->Send(f + (long long)(Dl - 1) * pl, cnt, ncclFloat, h->rank + 1, c->comm, h->stream));
-            FL_NCCL(h, c, c->Recv(f + (long long)(Dl + 1) * pl, cnt, ncclFloat, h->rank + 1, c->comm, h->stream));
+            FL_NCCL(h, c, c->Send(f + (long long)(Dl - 1) * pl, cnt, ncclFloat, h->rank + 1, c->comm, stream));
+            FL_NCCL(h, c, c->Recv(f + (long long)(Dl + 1) * pl, cnt, ncclFloat, h->rank + 1, c->comm, stream));
         }
     }
     FL_NCCL(h, c, c->GroupEnd());
     h->launches++;
     return 0;
 }
+
+int fl_halo_exchange(fluid_handle* h, int n, float* const* fields) { return fl_halo_exchange_on(h, n, fields, h->stream); }
 
 // all ranks' streams have reached this point before any continues (1-float all-reduce)
 int fl_barrier(fluid_handle* h)

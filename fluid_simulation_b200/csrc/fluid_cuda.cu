@@ -103,7 +103,7 @@ static fluid_handle* create_impl(int w, int hgt, int d, int speed, float dt, flo
     h->rank = rank; h->nranks = nranks;
     bool ok = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&h->dump_stream, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaStreamCreateWithFlags(&h->halo_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&h->halo_stream, cudaStreamNonBlocking, -1) == cudaSuccess &&   // edge sweeps + halo exchange go first
               cudaEventCreateWithFlags(&h->ev_frame_packed, cudaEventDisableTiming) == cudaSuccess &&
               cudaEventCreateWithFlags(&h->ev_frame_done, cudaEventDisableTiming) == cudaSuccess &&
               cudaEventCreateWithFlags(&h->ev_a, cudaEventDisableTiming) == cudaSuccess &&

@@ -15,6 +15,7 @@ int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid, const 
                    float a, float c, bool* handled);                     // tiled.cuh
 void fl_tiled_release(fluid_handle* h);                                  // tiled.cuh
 void fl_comm_release(fluid_handle* h);                                   // comm.cuh
+int fl_halo_exchange_on(fluid_handle* h, int n, float* const* fields, cudaStream_t stream);   // comm.cuh
 int fl_barrier(fluid_handle* h);                                         // comm.cuh
 
 static inline int fl_rebuild_flags(fluid_handle* h)

@@ -491,7 +491,7 @@ struct StreamState {
     std::map<std::pair<const float*, int>, CUtensorMap> maps;   // (field buffer, box rows * 1024 + box width) -> 3-D tensor map
     std::map<std::pair<int, int>, SwPlan> plans;                // (fields, owned rows per tile) -> segment table
     int zc_override = 0;
-    bool zigzag = true, unbatch = false;
+    bool zigzag = true, unbatch = false, overlap = true;
     int cfg = 0, dbg = 0, l2_ahead = 0;
 };
 
@@ -507,6 +507,7 @@ inline StreamState* sw_state(fluid_handle* h)
         if (const char* e = getenv("FLUID_TILED_ZC")) s->zc_override = atoi(e);
         if (const char* e = getenv("FLUID_SW_ZIGZAG")) s->zigzag = atoi(e) != 0;
         if (const char* e = getenv("FLUID_SW_UNBATCH")) s->unbatch = atoi(e) != 0;
+        if (const char* e = getenv("FLUID_SW_OVERLAP")) s->overlap = atoi(e) != 0;
         if (const char* e = getenv("FLUID_SW_CFG")) s->cfg = atoi(e);
         if (const char* e = getenv("FLUID_SW_DBG")) s->dbg = atoi(e);
         if (const char* e = getenv("FLUID_SW_L2AHEAD")) s->l2_ahead = atoi(e);
@@ -552,25 +553,43 @@ inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows
 // snapped onto it, because every segment pays 4 extra pipeline steps.
 #define SW_MINSEG 5
 #define SW_SEGCOST 4
-inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, SwPlan* out)
+// part 0 = all planes 1..Dl.  A z-slab whose halo exchange is overlapped with the sweep splits them:
+// part 1 = the SW_EDGE planes next to each interior slab face (one CTA per column and face; they run
+// first, on the halo stream, and the exchange follows them), part 2 = the planes in between.
+#define SW_EDGE 8
+inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPlan* out)
 {
     StreamState* s = sw_state(h);
-    auto key = std::make_pair(nb, ty * 16 + cps);
+    auto key = std::make_pair(nb, (ty * 16 + cps) * 4 + part);
     auto it = s->plans.find(key);
     if (it == s->plans.end()) {
         const Grid& g = h->g;
-        const int nty = (g.H + ty - 1) / ty, ncol = nb * nty, Dl = g.Dl;
+        const bool lo_face = h->rank > 0, hi_face = h->rank < h->nranks - 1;
+        // planes zoff+1 .. zoff+Dl of every column are distributed (part 0: zoff = 0, Dl = g.Dl)
+        const int zoff = (part == 2 && lo_face) ? SW_EDGE : 0;
+        const int Dl = part == 2 ? g.Dl - zoff - (hi_face ? SW_EDGE : 0) : g.Dl;
+        const int nty = (g.H + ty - 1) / ty, ncol = nb * nty;
         const long long T = (long long)ncol * Dl;
         std::vector<SwSeg> segs; std::vector<int> first;
+        if (part == 1) {
+            for (int c = 0; c < ncol; ++c) {
+                if (lo_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, 1, SW_EDGE, 0 }); }
+                if (hi_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, g.Dl - SW_EDGE + 1, g.Dl, 0 }); }
+            }
+        } else
         if (s->zc_override > 0) {                        // tests: fixed chunk height, one CTA per segment
             const int zc = s->zc_override;
             for (int c = 0; c < ncol; ++c)
                 for (int za = 1; za <= Dl; za += zc) {
                     first.push_back((int)segs.size());
-                    segs.push_back(SwSeg{ c, za, za + zc - 1 < Dl ? za + zc - 1 : Dl, 0 });
+                    segs.push_back(SwSeg{ c, zoff + za, zoff + (za + zc - 1 < Dl ? za + zc - 1 : Dl), 0 });
                 }
         } else {
             long long nc = (long long)h->sm_count * cps;
+            // overlapped exchange: the edge CTAs (part 1) run at the same time, and NCCL's copy kernel needs
+            // SMs of its own once they are done -- leave them room instead of queueing behind a full wave
+            if (part == 2) nc -= (long long)ncol * ((lo_face ? 1 : 0) + (hi_face ? 1 : 0));
+            if (nc < h->sm_count / 2) nc = h->sm_count / 2;
             if (nc > T / 8) nc = T / 8;                  // tiny grids: at least 8 planes per CTA
             if (nc < 1) nc = 1;
             // every CTA gets the same budget of pipeline steps: planes + SW_SEGCOST per segment it
@@ -586,7 +605,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, SwPlan* out)
                         if (rem - take > 0 && rem - take < SW_MINSEG) take = rem;       // no tiny leftovers
                         if (take < SW_MINSEG && take < rem) break;                      // no tiny starts
                         if (take <= 0) break;
-                        if (emit) segs.push_back(SwSeg{ c, z + 1, z + (int)take, 0 });
+                        if (emit) segs.push_back(SwSeg{ c, zoff + z + 1, zoff + z + (int)take, 0 });
                         left -= take + SW_SEGCOST; z += (int)take;
                         if (z == Dl) { ++c; z = 0; }
                     }
@@ -628,8 +647,12 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     FL_CUDA(h, cudaFuncSetAttribute(kjd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
     FL_CUDA(h, cudaFuncSetAttribute(kru, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
     FL_CUDA(h, cudaFuncSetAttribute(krd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
-    SwPlan plan;
-    if (int e = sw_get_plan(h, nb, GE::TY, CPS, &plan)) return e;
+    // z-slabs: the planes next to the slab faces are swept first on the halo stream and their exchange
+    // runs while the compute stream sweeps the planes in between
+    const bool overlap = h->nranks > 1 && s->overlap && s->zc_override == 0 && g.Dl >= 4 * SW_EDGE;
+    SwPlan plan, plan_edge;
+    if (int e = sw_get_plan(h, nb, GE::TY, CPS, overlap ? 2 : 0, &plan)) return e;
+    if (overlap) if (int e = sw_get_plan(h, nb, GE::TY, CPS, 1, &plan_edge)) return e;
     StreamArgs A;
     A.g = g; A.a = a; A.c_recip = 1.0f / c; A.flags = h->cflags;         // simulation.cpp:257
     A.nty = (g.H + GE::TY - 1) / GE::TY;
@@ -668,10 +691,25 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         }
         const bool down = s->zigzag && (k & 1);          // odd sweeps stream downwards (L2 reuse)
         auto kern = jacobi ? (down ? kjd : kju) : (down ? krd : kru);
+        if (overlap) {
+            // ev_a = "the in-between planes of the previous sweep (or whatever preceded the solve) are done"
+            if (k == 0) FL_CUDA(h, cudaEventRecord(h->ev_a, h->stream));
+            FL_CUDA(h, cudaStreamWaitEvent(h->halo_stream, h->ev_a, 0));
+            StreamArgs E = A; E.segs = plan_edge.segs; E.seg_first = plan_edge.seg_first;
+            kern<<<plan_edge.nctas, GE::THREADS, GE::SMEM, h->halo_stream>>>(E);
+            FL_CHECK_LAUNCH(h);
+        }
         kern<<<plan.nctas, GE::THREADS, GE::SMEM, h->stream>>>(A);
         FL_CHECK_LAUNCH(h);
         for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
-        if (h->nranks > 1) if (int e = fl_halo_exchange(h, nb, cur)) return e;     // two planes each way
+        if (overlap) {
+            if (int e = fl_halo_exchange_on(h, nb, cur, h->halo_stream)) return e;   // two planes each way
+            FL_CUDA(h, cudaEventRecord(h->ev_b, h->halo_stream));
+            FL_CUDA(h, cudaEventRecord(h->ev_a, h->stream));
+            FL_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_b, 0));                  // next sweep sees the halos
+        } else if (h->nranks > 1) {
+            if (int e = fl_halo_exchange(h, nb, cur)) return e;
+        }
     }
     if (pin) {
         cudaStreamAttrValue av = {};

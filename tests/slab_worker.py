@@ -35,7 +35,7 @@ def main():
 
     failures = 0
     cases = [("rb", SOLVER_RB, ORDER_RB), ("jacobi", SOLVER_JACOBI, ORDER_JACOBI)]
-    shapes = [(24, 16, 12), (128, 30, 17), (130, 9, 9), (256, 40, 4 * world + 3)]
+    shapes = [(24, 16, 12), (128, 30, 17), (130, 9, 9), (256, 40, 4 * world + 3), (132, 20, 35 * world + 1)]
     for name, flag, order in cases:
         for (w, h, d) in shapes:
             acc = 4
