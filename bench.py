@@ -276,6 +276,9 @@ def run_e2e(sim, args, w, h, d, mask, barrier, reduce_max, rank, world):
     xyz_p = sim.pinned_array(xyz.shape, np.int32); xyz_p[...] = xyz
     amt_p = sim.pinned_array((len(xyz),), np.float32); amt_p[...] = 0.001
     steps = max(2, min(args.steps, 10))
+    # one-time setup outside the timed region, like the reference opening its files: the pinned frame
+    # buffers (cudaHostAlloc of 4 x 69 MB takes longer than a whole step) and the device staging
+    sim.dump_frame_async((True, False, True, True, True)); sim.frame_wait()
     barrier()
     t0 = time.perf_counter()
     sim.set("obs", mask)                                  # obstacle mask H2D (once, amortised)

@@ -126,3 +126,47 @@ __device__ __forceinline__ void fl_store_bounded(const Grid& g, float* __restric
         }
     }
 }
+
+// ---- lean form of the same epilogue for FULL quads (x0 + 3 <= W) ------------------------------------
+// The face tests are folded into edge bits that a kernel writing several fields computes once per
+// quad; away from the faces (edge == 0) the epilogue is four selects and one 16-byte store.
+#define FL_XLO 1u
+#define FL_XHI 2u
+#define FL_YLO 4u
+#define FL_YHI 8u
+#define FL_ZLO 16u
+#define FL_ZHI 32u
+
+__device__ __forceinline__ unsigned fl_edge_bits(const Grid& g, int x0, int y, int zl)
+{
+    const int gz = g.zlo + zl - 1;
+    return (x0 == 1 ? FL_XLO : 0u) | (x0 + 3 == g.W ? FL_XHI : 0u) | (y == 1 ? FL_YLO : 0u) |
+           (y == g.H ? FL_YHI : 0u) | (gz == 1 ? FL_ZLO : 0u) | (gz == g.D ? FL_ZHI : 0u);
+}
+
+// f4 = the four flag bytes of the quad (little endian: lane 0 in the low byte)
+__device__ __forceinline__ void fl_store_quad(const Grid& g, float* __restrict__ out, long long c, const float4& raw,
+                                              unsigned f4, int b, unsigned edge)
+{
+    const unsigned t = f4 & (fl_zero_mask(b) * 0x01010101u);
+    float4 v;
+    v.x = (t & 0x000000ffu) ? 0.0f : raw.x;
+    v.y = (t & 0x0000ff00u) ? 0.0f : raw.y;
+    v.z = (t & 0x00ff0000u) ? 0.0f : raw.z;
+    v.w = (t & 0xff000000u) ? 0.0f : raw.w;
+    st4(out + c, v);
+    if (edge) {
+        if (edge & FL_XLO) out[c - 1] = (b == 1) ? -raw.x : raw.x;            // simulation.cpp:189
+        if (edge & FL_XHI) out[c + 4] = raw.w;                                // :191 outflow copy
+        if (edge & (FL_YLO | FL_YHI)) {                                       // :198-201
+            const float4 gy = (b == 2) ? make_float4(-raw.x, -raw.y, -raw.z, -raw.w) : raw;
+            if (edge & FL_YLO) st4(out + c - g.pitch, gy);
+            if (edge & FL_YHI) st4(out + c + g.pitch, gy);
+        }
+        if (edge & (FL_ZLO | FL_ZHI)) {                                       // :208-214
+            const float4 gz = (b == 3) ? make_float4(-raw.x, -raw.y, -raw.z, -raw.w) : raw;
+            if (edge & FL_ZLO) st4(out + c - g.plane, gz);
+            if (edge & FL_ZHI) st4(out + c + g.plane, gz);
+        }
+    }
+}

@@ -66,23 +66,24 @@ __global__ void __launch_bounds__(256) k_stats_partial(Grid g, int zl_first, int
                                                        const float* __restrict__ vz,
                                                        double* __restrict__ partial)
 {
+    // one x-row of the padded volume per block iteration: the division by the row length happens once
+    // per row, not once per cell (the kernel was bound by integer divides)
     const int Wp = g.W + 2;
-    const long long n = (long long)Wp * g.rows * (zl_last - zl_first + 1);
+    const long long nrows = (long long)g.rows * (zl_last - zl_first + 1);
     double s = 0.0;
     float mn[4] = { FLT_MAX, FLT_MAX, FLT_MAX, FLT_MAX }, mx[4] = { -FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX };
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n;
-         t += (long long)gridDim.x * blockDim.x) {
-        int x = (int)(t % Wp);
-        long long r = t / Wp;
-        int y = (int)(r % g.rows);
-        int zl = zl_first + (int)(r / g.rows);
-        long long c = fl_idx(g, x, y, zl);
-        float d = dens[c], a = vx[c], b = vy[c], e = vz[c];
-        s += (double)d;
-        mn[0] = fminf(mn[0], d); mx[0] = fmaxf(mx[0], d);
-        mn[1] = fminf(mn[1], a); mx[1] = fmaxf(mx[1], a);
-        mn[2] = fminf(mn[2], b); mx[2] = fmaxf(mx[2], b);
-        mn[3] = fminf(mn[3], e); mx[3] = fmaxf(mx[3], e);
+    for (long long r = blockIdx.x; r < nrows; r += gridDim.x) {
+        const int y = (int)(r % g.rows), zl = zl_first + (int)(r / g.rows);
+        const long long c0 = fl_idx(g, 0, y, zl);
+        for (int x = threadIdx.x; x < Wp; x += blockDim.x) {
+            const long long c = c0 + x;
+            float d = dens[c], a = vx[c], b = vy[c], e = vz[c];
+            s += (double)d;
+            mn[0] = fminf(mn[0], d); mx[0] = fmaxf(mx[0], d);
+            mn[1] = fminf(mn[1], a); mx[1] = fmaxf(mx[1], a);
+            mn[2] = fminf(mn[2], b); mx[2] = fmaxf(mx[2], b);
+            mn[3] = fminf(mn[3], e); mx[3] = fmaxf(mx[3], e);
+        }
     }
     block_fold_stats(s, mn, mx, partial + (long long)blockIdx.x * FL_NSTAT);
 }

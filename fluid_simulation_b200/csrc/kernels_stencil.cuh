@@ -123,13 +123,14 @@ __global__ void __launch_bounds__(256) k_divergence(Grid g, const float* __restr
     fl_store_bounded(g, p, flags, 0, q.x0, q.y, q.zl, zero);
 }
 
-// one-sided / central pressure difference (simulation.cpp:328-336 and the y, z copies)
-__device__ __forceinline__ float fl_axis_grad(bool po, bool mo, float pp, float pc, float pm, float h)
+// one-sided / central pressure difference (simulation.cpp:328-336 and the y, z copies) in select
+// form: both open -> (p+ - p-)/(2h); only + -> (p+ - p)/h; only - -> (p - p-)/h; none -> 0.
+// One division per axis instead of three divergent ones (the kernel was issue bound on them).
+__device__ __forceinline__ float fl_axis_grad(bool po, bool mo, float pp, float pc, float pm, float h, float h2)
 {
-    if (po && mo) return (pp - pm) / (2.0f * h);
-    if (po)       return (pp - pc) / h;
-    if (mo)       return (pc - pm) / h;
-    return 0.0f;
+    const float hi = po ? pp : pc, lo = mo ? pm : pc;
+    const float q = (hi - lo) / ((po && mo) ? h2 : h);
+    return (po || mo) ? q : 0.0f;
 }
 
 // ---- project part 3: v -= grad p on fluid cells, then setBounds(1..3) (:322-361) -------------
@@ -141,24 +142,35 @@ __global__ void __launch_bounds__(256) k_gradient(Grid g, const float* __restric
     QuadPos qp = fl_quad_pos(g, 1 + blockIdx.z);
     if (!qp.valid) return;
     const long long c = fl_idx(g, qp.x0, qp.y, qp.zl);
-    const uchar4 f4 = ldf4(flags + c);
-    const unsigned fl[4] = { f4.x, f4.y, f4.z, f4.w };
+    const unsigned f4 = *reinterpret_cast<const unsigned*>(flags + c);
+    const unsigned fl[4] = { f4 & 0xffu, (f4 >> 8) & 0xffu, (f4 >> 16) & 0xffu, f4 >> 24 };
     Quad7 q; fl_load_quad7(g, p, c, q);
     const float4 ax = ld4(vx + c), ay = ld4(vy + c), az = ld4(vz + c);
     float rx[4] = { ax.x, ax.y, ax.z, ax.w }, ry[4] = { ay.x, ay.y, ay.z, ay.w },
           rz[4] = { az.x, az.y, az.z, az.w };
+    const float h2 = 2.0f * h;                                    // :330 (2.0f * h)
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        if (fl[i] & FL_SOLID) continue;                           // :326 solids keep their value
-        float pxp = (i == 3) ? q.xp : q.c[i + 1];
-        float pxm = (i == 0) ? q.xm : q.c[i - 1];
-        rx[i] -= fl_axis_grad(fl[i] & FL_OPEN_XP, fl[i] & FL_OPEN_XM, pxp, q.c[i], pxm, h);
-        ry[i] -= fl_axis_grad(fl[i] & FL_OPEN_YP, fl[i] & FL_OPEN_YM, q.yp[i], q.c[i], q.ym[i], h);
-        rz[i] -= fl_axis_grad(fl[i] & FL_OPEN_ZP, fl[i] & FL_OPEN_ZM, q.zp[i], q.c[i], q.zm[i], h);
+        const float pxp = (i == 3) ? q.xp : q.c[i + 1];
+        const float pxm = (i == 0) ? q.xm : q.c[i - 1];
+        const float gx = fl_axis_grad(fl[i] & FL_OPEN_XP, fl[i] & FL_OPEN_XM, pxp, q.c[i], pxm, h, h2);
+        const float gy = fl_axis_grad(fl[i] & FL_OPEN_YP, fl[i] & FL_OPEN_YM, q.yp[i], q.c[i], q.ym[i], h, h2);
+        const float gz = fl_axis_grad(fl[i] & FL_OPEN_ZP, fl[i] & FL_OPEN_ZM, q.zp[i], q.c[i], q.zm[i], h, h2);
+        const bool solid = fl[i] & FL_SOLID;                      // :326 solids keep their value
+        rx[i] = solid ? rx[i] : rx[i] - gx;
+        ry[i] = solid ? ry[i] : ry[i] - gy;
+        rz[i] = solid ? rz[i] : rz[i] - gz;
     }
-    fl_store_bounded(g, vx, flags, 1, qp.x0, qp.y, qp.zl, rx);
-    fl_store_bounded(g, vy, flags, 2, qp.x0, qp.y, qp.zl, ry);
-    fl_store_bounded(g, vz, flags, 3, qp.x0, qp.y, qp.zl, rz);
+    if (qp.x0 + 3 <= g.W) {
+        const unsigned edge = fl_edge_bits(g, qp.x0, qp.y, qp.zl);
+        fl_store_quad(g, vx, c, make_float4(rx[0], rx[1], rx[2], rx[3]), f4, 1, edge);
+        fl_store_quad(g, vy, c, make_float4(ry[0], ry[1], ry[2], ry[3]), f4, 2, edge);
+        fl_store_quad(g, vz, c, make_float4(rz[0], rz[1], rz[2], rz[3]), f4, 3, edge);
+    } else {                                                      // ragged last quad of a row
+        fl_store_bounded(g, vx, flags, 1, qp.x0, qp.y, qp.zl, rx);
+        fl_store_bounded(g, vy, flags, 2, qp.x0, qp.y, qp.zl, ry);
+        fl_store_bounded(g, vz, flags, 3, qp.x0, qp.y, qp.zl, rz);
+    }
 }
 
 // ---- advect(b, field, prev) + setBounds (simulation.cpp:367-424) -----------------------------
@@ -167,13 +179,14 @@ __global__ void __launch_bounds__(256) k_gradient(Grid g, const float* __restric
 // velocity of component b comes from prev (:380-382), the other two from the current fields.
 struct GatherSrc { const float* base[8]; int zlo[8]; int dl[8]; int n; };
 
-__device__ __forceinline__ float fl_gather(const Grid& g, const GatherSrc& s, int x, int y, int gz)
+// pointer to cell (0, 0) of global plane gz: the plane lives on the slab with zlo <= gz < zlo+dl
+// (ghost planes 0 / D+1 on the end slabs)
+__device__ __forceinline__ const float* fl_gather_plane(const Grid& g, const GatherSrc& s, int gz)
 {
-    // global plane gz lives on the slab with zlo <= gz < zlo+dl (ghost planes 0 / D+1 on the ends)
     int r = 0;
 #pragma unroll 1
     for (int k = 0; k < s.n - 1; ++k) if (gz >= s.zlo[k] + s.dl[k]) r = k + 1;
-    return __ldg(s.base[r] + fl_idx(g, x, y, gz - s.zlo[r] + 1));
+    return s.base[r] + (FL_XOFF + (long long)(gz - s.zlo[r] + 1) * g.plane);
 }
 
 __device__ __forceinline__ float fl_clamp(float v, float lo, float hi)       // std::clamp
@@ -213,10 +226,11 @@ __global__ void __launch_bounds__(256) k_advect(Grid g, int b, float* __restrict
         zb = fl_clamp(zb, 0.5f, fD + 0.5f);
         const int i0 = (int)floorf(xb), j0 = (int)floorf(yb), k0 = (int)floorf(zb);   // :392-397
         const float sx = xb - (float)i0, sy = yb - (float)j0, sz = zb - (float)k0;    // :399-401
-        const float c000 = fl_gather(g, src, i0, j0, k0),     c100 = fl_gather(g, src, i0 + 1, j0, k0);
-        const float c010 = fl_gather(g, src, i0, j0 + 1, k0), c110 = fl_gather(g, src, i0 + 1, j0 + 1, k0);
-        const float c001 = fl_gather(g, src, i0, j0, k0 + 1),     c101 = fl_gather(g, src, i0 + 1, j0, k0 + 1);
-        const float c011 = fl_gather(g, src, i0, j0 + 1, k0 + 1), c111 = fl_gather(g, src, i0 + 1, j0 + 1, k0 + 1);
+        // the 8 corners: two planes (k0, k0+1, possibly on different slabs), 2 x 2 cells in each
+        const float* __restrict__ q0 = fl_gather_plane(g, src, k0) + (i0 + j0 * g.pitch);
+        const float* __restrict__ q1 = fl_gather_plane(g, src, k0 + 1) + (i0 + j0 * g.pitch);
+        const float c000 = __ldg(q0), c100 = __ldg(q0 + 1), c010 = __ldg(q0 + g.pitch), c110 = __ldg(q0 + g.pitch + 1);
+        const float c001 = __ldg(q1), c101 = __ldg(q1 + 1), c011 = __ldg(q1 + g.pitch), c111 = __ldg(q1 + g.pitch + 1);
         const float c00 = c000 * (1.0f - sx) + c100 * sx;                    // :412-415
         const float c01 = c001 * (1.0f - sx) + c101 * sx;
         const float c10 = c010 * (1.0f - sx) + c110 * sx;
@@ -225,5 +239,9 @@ __global__ void __launch_bounds__(256) k_advect(Grid g, int b, float* __restrict
         const float c1 = c01 * (1.0f - sy) + c11 * sy;
         raw[i] = c0 * (1.0f - sz) + c1 * sz;                                 // :420
     }
-    fl_store_bounded(g, field, flags, b, qp.x0, qp.y, qp.zl, raw);
+    if (qp.x0 + 3 <= g.W)
+        fl_store_quad(g, field, c, make_float4(raw[0], raw[1], raw[2], raw[3]),
+                      *reinterpret_cast<const unsigned*>(flags + c), b, fl_edge_bits(g, qp.x0, qp.y, qp.zl));
+    else
+        fl_store_bounded(g, field, flags, b, qp.x0, qp.y, qp.zl, raw);
 }
