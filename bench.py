@@ -45,17 +45,46 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons while the timed region runs."""
+    """SM clock + throttle reasons while the timed region runs: NVML polled every few ms (the region is
+    ~0.1 s long, too short for nvidia-smi's process start-up), nvidia-smi as the fallback."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, gpu=0):
+    def __init__(self, gpu=0, uuid=None):
         super().__init__(daemon=True)
-        self.gpu, self.samples, self.stop_flag = gpu, [], False
+        self.gpu, self.samples, self.stop_flag, self.source = gpu, [], False, "nvidia-smi"
+        self.nv = self.dev = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                self.dev = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode()) if uuid else None
+            except Exception:
+                self.dev = None
+            if self.dev is None:
+                self.dev = pynvml.nvmlDeviceGetHandleByIndex(gpu)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM))
+            self.nv, self.source = pynvml, "nvml"
+        except Exception:
+            self.nv = None
+
+    def sample_nvml(self):
+        nv = self.nv
+        mhz = nv.nvmlDeviceGetClockInfo(self.dev, nv.NVML_CLOCK_SM)
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+            else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.dev)
+        bits = [nv.nvmlClocksThrottleReasonHwSlowdown, nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                nv.nvmlClocksThrottleReasonSwThermalSlowdown, nv.nvmlClocksThrottleReasonSwPowerCap]
+        return [str(mhz), str(self.max_mhz)] + ["Active" if r & b else "Not Active" for b in bits]
 
     def run(self):
         while not self.stop_flag:
             try:
+                if self.nv is not None:
+                    self.samples.append(self.sample_nvml())
+                    time.sleep(0.004)
+                    continue
                 out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True,
                                      timeout=5).stdout.strip()
@@ -63,16 +92,29 @@ class ClockSampler(threading.Thread):
                     self.samples.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.05)
 
     def summary(self):
         self.stop_flag = True
         sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
         mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
+        reasons = sorted({n for s in self.samples for n, v in zip(self.NAMES, s[2:6]) if v.lower().startswith("active")})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": self.source}
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one single-field k_sweep_stream launch at 256^3, from
+    the newest committed `ncu --set full` summary under profiles/ (bytes; None if there is none)."""
+    import glob
+    import re
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full.txt")), reverse=True):
+        txt = open(path).read()
+        rd = re.search(r"dram__bytes_read\.sum = ([0-9.]+) Mbyte", txt)
+        wr = re.search(r"dram__bytes_write\.sum = ([0-9.]+) Mbyte", txt)
+        if rd and wr and "k_sweep_stream" in txt:
+            return (float(rd.group(1)) + float(wr.group(1))) * 1e6, os.path.relpath(path, ROOT)
+    return None, None
 
 
 def workload(n_gpus, args):
@@ -195,7 +237,10 @@ def run_ours(args):
     # ---- device-resident timing ------------------------------------------------------------
     sim.run_iterations(args.warmup)
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
+    vis = [v.strip() for v in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if v.strip()]
+    entry = vis[local] if local < len(vis) else str(local)          # NVML numbers physical devices
+    sampler = (ClockSampler(int(entry)) if entry.isdigit() else ClockSampler(local, entry[4:] if entry.startswith("GPU-") else None)) \
+        if rank == 0 else None
     if sampler:
         sampler.start()
     sim.profile(True); sim.profile_read()
@@ -219,9 +264,12 @@ def run_ours(args):
     sweep_bytes = 12.0 * local_cells                      # x in, rhs in, x out per cell per sweep
     achieved = sweep_bytes * field_sweeps / (solve_ms * 1e-3) / 1e9 if solve_ms > 0 else 0.0
     step_bytes = bytes_per_cell_step(acc, args.elide) * local_cells
+    traffic, traffic_src = ncu_traffic()
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": None,
+        "traffic": traffic if (w, h, sim.d_local) == (W0, H0, D0) else None,
+        "traffic_source": f"{traffic_src}: dram read+write bytes of one single-field sweep launch "
+                          f"(algorithmic {sweep_bytes / 1e6:.1f} MB)" if traffic_src else None,
         "kernel": "linearSolver sweeps (12 B/cell/sweep algorithmic; CUDA events around every solve)",
         "peak_source": peak_src, "us_per_field_sweep": solve_ms * 1e3 / max(field_sweeps, 1),
         "solver_share_of_step": solve_ms / (ms if ms > 0 else 1.0),

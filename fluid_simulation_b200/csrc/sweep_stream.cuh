@@ -36,7 +36,7 @@
 #define SW_SMEM_MAX 232448               // 227 KB of dynamic shared memory per CTA on sm_100
 #define SW_SM_SMEM  233472               // 228 KB of shared memory per SM (each resident CTA also reserves 1 KB)
 
-struct SwSeg { int col, za, zb, pad; };     // column (batched field * row tiles + row tile), planes za..zb
+struct SwSeg { int col, za, zb, down; };    // column (batched field * row tiles + row tile), planes za..zb, streamed downwards?
 
 struct alignas(64) StreamArgs {
     CUtensorMap map[3];                  // source field of each batched solve (box SW_BOXW x BR x 1)
@@ -49,7 +49,7 @@ struct alignas(64) StreamArgs {
     Grid g;
     float a, c_recip;
     int nty;                             // row tiles per field
-    int l2_ahead;                        // L2 prefetch distance beyond the shared-memory ring, in planes (0 = off)
+    int flip;                            // 1 = this sweep streams every segment against its planned direction
     int dbg;                             // FLUID_SW_DBG timing experiments: 1 = no stores, 2 = no relaxation (results invalid)
 };
 
@@ -82,12 +82,6 @@ __device__ __forceinline__ void sw_tma_load_3d(void* dst, const CUtensorMap* map
         "[%0], [%1, {%2, %3, %4}], [%5];"
         ::"r"(sw_smem(dst)), "l"(reinterpret_cast<unsigned long long>(map)), "r"(c0), "r"(c1), "r"(c2),
           "r"(sw_smem(bar)) : "memory");
-}
-// L2-only prefetch of a box: hides the HBM latency of planes that have no shared-memory slot yet
-__device__ __forceinline__ void sw_tma_prefetch_3d(const CUtensorMap* map, int c0, int c1, int c2)
-{
-    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];"
-                 ::"l"(reinterpret_cast<unsigned long long>(map)), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 __device__ __forceinline__ void sw_fence_proxy_async()
 {
@@ -331,12 +325,115 @@ __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float*
     }
 }
 
-// MODE 0 = Jacobi, 1 = red-black (colour 0 = (x+y+z) even first); DIR = +1 streams every segment
-// upwards in z, -1 downwards.  The host alternates DIR from sweep to sweep: the planes a CTA wrote
-// last are the ones it reads first in the next sweep, while they are still in L2.
-// A CTA works through a short list of segments (column = batched field x row tile, planes za..zb);
-// the TMA ring and its mbarrier phases run on across segments.
+// One segment (planes za..zb of one column) streamed in direction DIR (+1 upwards in z, -1 downwards);
+// the TMA ring position and its mbarrier phase (s_iss, s_con, ph_con) run on from segment to segment.
 template <int TXW, int NP, int CPS, int MODE, int DIR>
+__device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, SwThread& t, float* const uring,
+                                           float* const vbuf, unsigned long long* const bars, int& s_iss, int& s_con,
+                                           unsigned& ph_con, const int tid, const int pr, const int rA, const int x0,
+                                           const bool lane_in, const unsigned exbits, const unsigned safe)
+{
+    using GE = SwGeom<TXW, NP, CPS>;
+    constexpr int BOXF = GE::BOXF, RBOXF = GE::RBOXF, SLOTF = GE::SLOTF, XSLOTF = GE::XSLOTF;
+    constexpr int NSLOT = GE::NSLOT;
+    const Grid& g = A.g;
+    const unsigned plane = (unsigned)g.plane;
+    const unsigned dplane = DIR > 0 ? plane : 0u - plane;
+    const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const int batch = sg.col / A.nty;
+    const int y0 = 1 + (sg.col - batch * A.nty) * GE::TY;        // first owned row (odd)
+    const int za = sg.za, zb = sg.zb;
+    const int lo = max(za - 2, g.zl_lo), hi = min(zb + 2, g.zl_hi);   // planes this segment reads
+    const int ps = DIR > 0 ? za - 1 : zb + 1;                    // first stage-0 plane
+    const int nsteps = zb - za + 3;
+    const bool has_behind = DIR > 0 ? (ps - 1 >= lo) : (ps + 1 <= hi);
+    const int first = has_behind ? ps - DIR : ps;                // first plane loaded, then first + DIR, ...
+    const int nplanes = (DIR > 0 ? hi - first : first - lo) + 1;
+    const int b = A.b[batch];
+    const unsigned zmask4 = fl_zero_mask(b) * 0x01010101u;
+    float* __restrict__ out = A.dst[batch];
+
+    // plane p -> ring slot s_iss.  Every thread tracks the ring position, so that the slot and barrier
+    // addresses stay warp-uniform; thread 0 alone arms the barrier and starts the copies.
+    auto issue = [&](int p) {
+        if (tid == 0) {
+            unsigned long long* bar = &bars[s_iss];
+            sw_mbar_expect_tx(bar, GE::TX_BYTES);
+            float* slot = uring + s_iss * SLOTF;
+#pragma unroll
+            for (int i = 0; i < TXW; ++i) {
+                // the tensor maps start at the allocation's plane -1, hence p + 1
+                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p + 1, bar);
+                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p + 1, bar);
+            }
+        }
+        if (++s_iss == NSLOT) s_iss = 0;
+    };
+    int issued = min(nplanes, NSLOT);                            // planes handed to TMA so far (uniform)
+    for (int j = 0; j < issued; ++j) issue(first + DIR * j);
+
+    // this thread's quad: cells x0..x0+3 of rows yA (even) and yB = yA + 1 (odd)
+    const int yA = y0 - 2 + rA, yB = yA + 1;
+    t.intA = lane_in && yA >= 1 && yA <= g.H;                    // row takes part in stage 0
+    t.intB = lane_in && yB >= 1 && yB <= g.H;
+    t.ownA = t.intA && pr >= 1;                                  // row is stored by this CTA
+    t.ownB = t.intB && pr <= NP - 2;
+    t.eA = exbits | (yA == 1 ? SW_YLO : 0u) | (yA == g.H ? SW_YHI : 0u);
+    t.eB = exbits | (yB == 1 ? SW_YLO : 0u) | (yB == g.H ? SW_YHI : 0u);
+    // element offsets (32-bit: the padded volume has < 2^32 cells).  Rows / lanes outside the
+    // grid read a harmless in-range cell instead of being predicated off.
+    t.oA = (t.intA ? (unsigned)fl_idx(g, x0, yA, 0) : safe) + (unsigned)ps * plane;
+    t.oB = (t.intB ? (unsigned)fl_idx(g, x0, yB, 0) : safe) + (unsigned)ps * plane;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { t.QA[i] = zero4; t.QB[i] = zero4; t.RA[i] = zero4; t.RB[i] = zero4; t.FA[i] = 0; t.FB[i] = 0; }
+
+    // prologue: own column of the plane behind ps (ring index 1) and of ps (index 2); flag bytes
+    // of the first plane that is stored
+    auto consume = [&]() -> const float* {                       // wait for the next plane in stream order
+        sw_mbar_wait(&bars[s_con], ph_con);
+        const float* s = uring + s_con * SLOTF;
+        if (++s_con == NSLOT) { s_con = 0; ph_con ^= 1u; }
+        return s;
+    };
+    if (has_behind) { const float* Ub = consume(); t.QA[1] = sw_lds4(Ub + t.offA); t.QB[1] = sw_lds4(Ub + t.offB); }
+    const float* Up = consume();
+    t.QA[2] = sw_lds4(Up + t.offA); t.QB[2] = sw_lds4(Up + t.offB);
+    t.FA[3] = *reinterpret_cast<const unsigned*>(A.flags + (t.oA + dplane));
+    t.FB[3] = *reinterpret_cast<const unsigned*>(A.flags + (t.oB + dplane));
+    __syncthreads();        // the slot of the plane behind ps is re-armed by the first step
+
+    int p = ps, step = 0;
+    int jc = has_behind ? 1 : 0;                                 // stream index of plane p
+    // No proxy fence before the barrier: the slot the next TMA overwrites was only READ through
+    // the generic proxy, and those reads are ordered before the issuing thread's TMA by the barrier.
+#define SW_STEP(U, E)                                                                                       \
+    {                                                                                                   \
+        if (step == nsteps) break;                                                                      \
+        if (issued < nplanes && issued - jc < NSLOT) {        /* a slot behind plane p is free */       \
+            issue(first + DIR * issued);                                                                \
+            ++issued;                                                                                   \
+        }                                                                                               \
+        t.oA += dplane; t.oB += dplane;                                                                 \
+        const bool has_next = DIR > 0 ? (p + 1 <= hi) : (p - 1 >= lo);                                  \
+        unsigned long long* bar_n = &bars[s_con];                                                       \
+        const unsigned ph_n = ph_con;                                                                   \
+        const float* Un = uring + s_con * SLOTF;                                                        \
+        if (has_next) { if (++s_con == NSLOT) { s_con = 0; ph_con ^= 1u; } }                            \
+        sw_step<BOXF, XSLOTF, MODE, DIR, U, E>(t, A, out, b, zmask4, p, za, zb, has_next, Up, Un, bar_n, \
+                                               ph_n, vbuf);                                             \
+        Up = Un; p += DIR; ++step; ++jc;                                                                \
+        __syncthreads();                                                                                \
+    }
+    if (((g.zlo + ps) & 1) == 0) { for (;;) { SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
+    else                         { for (;;) { SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
+#undef SW_STEP
+}
+
+// MODE 0 = Jacobi, 1 = red-black (colour 0 = (x+y+z) even first).  A CTA works through a short list
+// of segments (column = batched field x row tile, planes za..zb), each streamed in the direction the
+// plan gave it, reversed when A.flip is set.  The host flips every other sweep: the planes a CTA wrote
+// last are the ones it reads first in the next sweep, while they are still in L2.
+template <int TXW, int NP, int CPS, int MODE>
 __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __grid_constant__ StreamArgs A)
 {
     using GE = SwGeom<TXW, NP, CPS>;
@@ -369,109 +466,17 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
     t.pub_gl = lane == 0 && wx == 0;        t.pub_nl = lane == 0 && wx > 0;
     t.pub_gr = lane == 31 && wx == TXW - 1; t.pub_nr = lane == 31 && wx + 1 < TXW;
     const unsigned exbits = (x0 == 1 ? SW_XLO : 0u) | (x0 + 3 == g.W ? SW_XHI : 0u);
-    const unsigned plane = (unsigned)g.plane;
-    const unsigned dplane = DIR > 0 ? plane : 0u - plane;
     const unsigned safe = (unsigned)fl_idx(g, 1, 1, 0);
-    const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 
     int s_iss = 0;                                                   // ring slot the next TMA plane goes to
     int s_con = 0; unsigned ph_con = 0;                              // slot / mbarrier parity of the next plane consumed
 
     for (int si = A.seg_first[blockIdx.x]; si < A.seg_first[blockIdx.x + 1]; ++si) {
         const SwSeg sg = A.segs[si];
-        const int batch = sg.col / A.nty;
-        const int y0 = 1 + (sg.col - batch * A.nty) * GE::TY;        // first owned row (odd)
-        const int za = sg.za, zb = sg.zb;
-        const int lo = max(za - 2, g.zl_lo), hi = min(zb + 2, g.zl_hi);   // planes this segment reads
-        const int ps = DIR > 0 ? za - 1 : zb + 1;                    // first stage-0 plane
-        const int nsteps = zb - za + 3;
-        const bool has_behind = DIR > 0 ? (ps - 1 >= lo) : (ps + 1 <= hi);
-        const int first = has_behind ? ps - DIR : ps;                // first plane loaded, then first + DIR, ...
-        const int nplanes = (DIR > 0 ? hi - first : first - lo) + 1;
-        const int b = A.b[batch];
-        const unsigned zmask4 = fl_zero_mask(b) * 0x01010101u;
-        float* __restrict__ out = A.dst[batch];
-
-        auto issue = [&](int p) {                                    // plane p -> ring slot s_iss
-            unsigned long long* bar = &bars[s_iss];
-            sw_mbar_expect_tx(bar, GE::TX_BYTES);
-            float* slot = uring + s_iss * SLOTF;
-#pragma unroll
-            for (int i = 0; i < TXW; ++i) {
-                // the tensor maps start at the allocation's plane -1, hence p + 1
-                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p + 1, bar);
-                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p + 1, bar);
-            }
-            if (++s_iss == NSLOT) s_iss = 0;
-            // ... and the plane SW_L2_AHEAD steps further on starts its way from HBM into L2
-            const int pf = p + DIR * A.l2_ahead;
-            if (A.l2_ahead > 0 && pf >= lo && pf <= hi) {
-#pragma unroll
-                for (int i = 0; i < TXW; ++i) {
-                    sw_tma_prefetch_3d(&A.map[batch], 128 * i, y0 - 2, pf + 1);
-                    sw_tma_prefetch_3d(&A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, pf + 1);
-                }
-            }
-        };
-        int issued = min(nplanes, NSLOT);                            // planes handed to TMA so far (uniform)
-        if (tid == 0)
-            for (int j = 0; j < issued; ++j) issue(first + DIR * j);
-
-        // this thread's quad: cells x0..x0+3 of rows yA (even) and yB = yA + 1 (odd)
-        const int yA = y0 - 2 + rA, yB = yA + 1;
-        t.intA = lane_in && yA >= 1 && yA <= g.H;                    // row takes part in stage 0
-        t.intB = lane_in && yB >= 1 && yB <= g.H;
-        t.ownA = t.intA && pr >= 1;                                  // row is stored by this CTA
-        t.ownB = t.intB && pr <= NP - 2;
-        t.eA = exbits | (yA == 1 ? SW_YLO : 0u) | (yA == g.H ? SW_YHI : 0u);
-        t.eB = exbits | (yB == 1 ? SW_YLO : 0u) | (yB == g.H ? SW_YHI : 0u);
-        // element offsets (32-bit: the padded volume has < 2^32 cells).  Rows / lanes outside the
-        // grid read a harmless in-range cell instead of being predicated off.
-        t.oA = (t.intA ? (unsigned)fl_idx(g, x0, yA, 0) : safe) + (unsigned)ps * plane;
-        t.oB = (t.intB ? (unsigned)fl_idx(g, x0, yB, 0) : safe) + (unsigned)ps * plane;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { t.QA[i] = zero4; t.QB[i] = zero4; t.RA[i] = zero4; t.RB[i] = zero4; t.FA[i] = 0; t.FB[i] = 0; }
-
-        // prologue: own column of the plane behind ps (ring index 1) and of ps (index 2); flag bytes
-        // of the first plane that is stored
-        auto consume = [&]() -> const float* {                       // wait for the next plane in stream order
-            sw_mbar_wait(&bars[s_con], ph_con);
-            const float* s = uring + s_con * SLOTF;
-            if (++s_con == NSLOT) { s_con = 0; ph_con ^= 1u; }
-            return s;
-        };
-        if (has_behind) { const float* Ub = consume(); t.QA[1] = sw_lds4(Ub + t.offA); t.QB[1] = sw_lds4(Ub + t.offB); }
-        const float* Up = consume();
-        t.QA[2] = sw_lds4(Up + t.offA); t.QB[2] = sw_lds4(Up + t.offB);
-        t.FA[3] = *reinterpret_cast<const unsigned*>(A.flags + (t.oA + dplane));
-        t.FB[3] = *reinterpret_cast<const unsigned*>(A.flags + (t.oB + dplane));
-        __syncthreads();        // the slot of the plane behind ps is re-armed by the first step
-
-        int p = ps, step = 0;
-        int jc = has_behind ? 1 : 0;                                 // stream index of plane p
-        // No proxy fence before the barrier: the slot the next TMA overwrites was only READ through
-        // the generic proxy, and those reads are ordered before the issuing thread's TMA by the barrier.
-#define SW_STEP(U, E)                                                                                       \
-        {                                                                                                   \
-            if (step == nsteps) break;                                                                      \
-            if (issued < nplanes && issued - jc < NSLOT) {        /* a slot behind plane p is free */       \
-                if (tid == 0) issue(first + DIR * issued);                                                  \
-                ++issued;                                                                                   \
-            }                                                                                               \
-            t.oA += dplane; t.oB += dplane;                                                                 \
-            const bool has_next = DIR > 0 ? (p + 1 <= hi) : (p - 1 >= lo);                                  \
-            unsigned long long* bar_n = &bars[s_con];                                                       \
-            const unsigned ph_n = ph_con;                                                                   \
-            const float* Un = uring + s_con * SLOTF;                                                        \
-            if (has_next) { if (++s_con == NSLOT) { s_con = 0; ph_con ^= 1u; } }                            \
-            sw_step<BOXF, XSLOTF, MODE, DIR, U, E>(t, A, out, b, zmask4, p, za, zb, has_next, Up, Un, bar_n, \
-                                                   ph_n, vbuf);                                             \
-            Up = Un; p += DIR; ++step; ++jc;                                                                \
-            __syncthreads();                                                                                \
-        }
-        if (((g.zlo + ps) & 1) == 0) { for (;;) { SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
-        else                         { for (;;) { SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
-#undef SW_STEP
+        if ((sg.down ^ A.flip) & 1)
+            sw_segment<TXW, NP, CPS, MODE, -1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, x0, lane_in, exbits, safe);
+        else
+            sw_segment<TXW, NP, CPS, MODE, 1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, x0, lane_in, exbits, safe);
     }
     if (A.nty < 0) A.dst[0][0] = __uint_as_float(t.sink);            // never taken: keeps t.sink observable
 }
@@ -492,7 +497,8 @@ struct StreamState {
     std::map<std::pair<int, int>, SwPlan> plans;                // (fields, owned rows per tile) -> segment table
     int zc_override = 0;
     bool zigzag = true, unbatch = false, overlap = true;
-    int cfg = 0, dbg = 0, l2_ahead = 0;
+    int cfg = 0, dbg = 0;
+    int plan_mode = 2, plan_min_fill = 85;                      // FLUID_SW_PLAN: 0 = auto, 1 = uniform ranges, 2 = balanced budget
 };
 
 inline StreamState* sw_state(fluid_handle* h)
@@ -510,7 +516,8 @@ inline StreamState* sw_state(fluid_handle* h)
         if (const char* e = getenv("FLUID_SW_OVERLAP")) s->overlap = atoi(e) != 0;
         if (const char* e = getenv("FLUID_SW_CFG")) s->cfg = atoi(e);
         if (const char* e = getenv("FLUID_SW_DBG")) s->dbg = atoi(e);
-        if (const char* e = getenv("FLUID_SW_L2AHEAD")) s->l2_ahead = atoi(e);
+        if (const char* e = getenv("FLUID_SW_PLAN")) s->plan_mode = atoi(e);
+        if (const char* e = getenv("FLUID_SW_PLAN_FILL")) s->plan_min_fill = atoi(e);
         h->tiled = s;
     }
     return (StreamState*)h->tiled;
@@ -592,6 +599,22 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
             if (nc < h->sm_count / 2) nc = h->sm_count / 2;
             if (nc > T / 8) nc = T / 8;                  // tiny grids: at least 8 planes per CTA
             if (nc < 1) nc = 1;
+            // Uniform plan: every column is cut into the same S ranges and one CTA streams range k of a
+            // column, upwards for even k, downwards for odd k.  Neighbouring row tiles are then on the same
+            // plane at the same time and the ranges of a column reach their shared boundary together, so
+            // halo rows and halo planes are L2 hits instead of second HBM reads.  It leaves nc - S*ncol
+            // SMs idle, which the HBM-bound kernel tolerates up to a point (plan_min_fill, per cent).
+            const long long S = nc / ncol;
+            const bool uniform = s->plan_mode == 1 ||
+                (s->plan_mode == 0 && S >= 1 && S * ncol * 100 >= nc * s->plan_min_fill && Dl / (S > 0 ? S : 1) >= 3 * SW_MINSEG);
+            if (uniform && S >= 1 && Dl / S >= 1) {
+                for (long long k = 0; k < S; ++k)
+                    for (int c = 0; c < ncol; ++c) {
+                        const int z0 = (int)(k * Dl / S), z1 = (int)((k + 1) * Dl / S);
+                        first.push_back((int)segs.size());
+                        segs.push_back(SwSeg{ c, zoff + z0 + 1, zoff + z1, (int)(k & 1) });
+                    }
+            } else {
             // every CTA gets the same budget of pipeline steps: planes + SW_SEGCOST per segment it
             // starts.  The smallest budget with which nc CTAs cover all columns is found by bisection.
             auto build = [&](long long budget, bool emit) -> bool {
@@ -619,6 +642,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
                 if (build(mid, false)) hi_b = mid; else lo_b = mid;
             }
             build(hi_b, true);
+            }
         }
         first.push_back((int)segs.size());
         SwPlan pl;
@@ -641,12 +665,8 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     using GE = SwGeom<TXW, NP, CPS>;
     const Grid& g = h->g;
     StreamState* s = sw_state(h);
-    auto kju = k_sweep_stream<TXW, NP, CPS, 0, 1>; auto kjd = k_sweep_stream<TXW, NP, CPS, 0, -1>;
-    auto kru = k_sweep_stream<TXW, NP, CPS, 1, 1>; auto krd = k_sweep_stream<TXW, NP, CPS, 1, -1>;
-    FL_CUDA(h, cudaFuncSetAttribute(kju, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
-    FL_CUDA(h, cudaFuncSetAttribute(kjd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
-    FL_CUDA(h, cudaFuncSetAttribute(kru, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
-    FL_CUDA(h, cudaFuncSetAttribute(krd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
+    auto kern = jacobi ? k_sweep_stream<TXW, NP, CPS, 0> : k_sweep_stream<TXW, NP, CPS, 1>;
+    FL_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
     // z-slabs: the planes next to the slab faces are swept first on the halo stream and their exchange
     // runs while the compute stream sweeps the planes in between
     const bool overlap = h->nranks > 1 && s->overlap && s->zc_override == 0 && g.Dl >= 4 * SW_EDGE;
@@ -657,7 +677,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     A.g = g; A.a = a; A.c_recip = 1.0f / c; A.flags = h->cflags;         // simulation.cpp:257
     A.nty = (g.H + GE::TY - 1) / GE::TY;
     A.segs = plan.segs; A.seg_first = plan.seg_first;
-    A.dbg = s->dbg; A.l2_ahead = s->l2_ahead;
+    A.dbg = s->dbg;
 
     float* cur[3]; float* alt[3];
     for (int i = 0; i < nb; ++i) {
@@ -689,8 +709,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
             if (int e = sw_get_map(h, cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
             A.dst[i] = alt[i];
         }
-        const bool down = s->zigzag && (k & 1);          // odd sweeps stream downwards (L2 reuse)
-        auto kern = jacobi ? (down ? kjd : kju) : (down ? krd : kru);
+        A.flip = (s->zigzag && (k & 1)) ? 1 : 0;         // odd sweeps stream the other way (L2 reuse)
         if (overlap) {
             // ev_a = "the in-between planes of the previous sweep (or whatever preceded the solve) are done"
             if (k == 0) FL_CUDA(h, cudaEventRecord(h->ev_a, h->stream));
@@ -729,7 +748,7 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
     const Grid& g = h->g;
     const unsigned solver = h->flags & FLUID_SOLVER_MASK;
     if (solver != FLUID_SOLVER_RB && solver != FLUID_SOLVER_JACOBI) return 0;
-    if ((g.W & 3) || g.W > 512) return 0;                // quads must not straddle the x = W+1 ghost
+    if ((g.W & 3) || g.W > 1024) return 0;                // quads must not straddle the x = W+1 ghost
     if (!(h->flags & FLUID_TILED_ALWAYS) && (g.W < 64 || g.H < 8 || g.Dl < 4)) return 0;
     StreamState* s = sw_state(h);
     if (!s->encode) return fl_fail(h, FLUID_E_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
@@ -746,7 +765,8 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
             else if (s->cfg == 2) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac);
             else if (s->cfg == 3) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac);
             else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac);
-        } else                 e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac);
+        } else if (g.W <= 512) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac);
+        else                   e = sw_run<8, 2, 1>(h, per, bb, ff, pp, a, c, jac);   // two owned rows: x re-read twice
         if (e) return e;
     }
     *handled = true;

@@ -1,6 +1,6 @@
 """The TMA-fed register-streaming sweep kernel (csrc/sweep_stream.cuh) against the ordering-matched
 CPU oracle, bit-exact, over warp-column, row-tile, ragged and multi-chunk shapes; and against the
-simple global-memory kernels (FLUID_NO_TILED) on a larger grid.  Shapes with W % 4 != 0 or W > 512
+simple global-memory kernels (FLUID_NO_TILED) on a larger grid.  Shapes with W % 4 != 0 or W > 1024
 exercise the documented hand-over to the simple kernels under FLUID_TILED_ALWAYS."""
 import os
 
@@ -14,11 +14,12 @@ pytestmark = pytest.mark.gpu
 
 TILED_ALWAYS, NO_TILED = 0x40, 0x20
 SOLVERS = [("rb", 0x0, ORDER_RB), ("jacobi", 0x1, ORDER_JACOBI)]
-# W around the 128-cell warp columns (1, 2, 4 columns), H around the row-tile heights (30 / 16 / 6
-# owned rows), D around chunk sizes
+# W around the 128-cell warp columns (1, 2, 4, 8 columns), H around the row-tile heights (30 / 14 /
+# 6 / 2 owned rows), D around chunk sizes
 SHAPES = [(130, 33, 9), (128, 30, 8), (127, 31, 17), (257, 61, 12), (100, 29, 5), (24, 16, 12),
           (5, 3, 2), (1, 1, 1), (260, 8, 4), (129, 90, 3), (256, 40, 20), (512, 13, 9), (384, 20, 7),
-          (64, 64, 33), (132, 70, 6), (8, 2, 2), (4, 1, 1), (252, 17, 5), (516, 6, 3)]
+          (64, 64, 33), (132, 70, 6), (8, 2, 2), (4, 1, 1), (252, 17, 5), (516, 6, 3),
+          (1024, 9, 4), (772, 5, 6), (1028, 4, 3)]
 
 
 def pair(w, h, d, acc, flag, order, seed=7):
@@ -71,3 +72,16 @@ def test_tiled_equals_simple_kernels_256(name, flag, order):
     a.set("obs", obs); b.set("obs", obs)
     a.run_iterations(2); b.run_iterations(2)
     assert_bitwise(a.state(), b.state(), FIELD_NAMES, f"tiled vs simple [{name}]")
+
+
+@pytest.mark.parametrize("name,flag,order", SOLVERS)
+def test_tiled_equals_simple_kernels_wide(name, flag, order):
+    """A/B at the W = 1024 plane of BASELINE config 5 (eight warp columns, two owned rows)."""
+    from fluid_simulation_b200 import Simulation, masks
+    w, h, d, acc = 1024, 96, 20, 6
+    obs = masks.sphere(w, h, d)
+    a = Simulation(w, h, d, 1, acc=acc, flags=flag)
+    b = Simulation(w, h, d, 1, acc=acc, flags=flag | NO_TILED)
+    a.set("obs", obs); b.set("obs", obs)
+    a.run_iterations(2); b.run_iterations(2)
+    assert_bitwise(a.state(), b.state(), FIELD_NAMES, f"tiled vs simple, W=1024 [{name}]")
