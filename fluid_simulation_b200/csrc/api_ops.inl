@@ -72,19 +72,27 @@ int fluid_comm_init(fluid_handle* h, const char* nccl_lib_path, const char id_by
     return 0;
 }
 
-int fluid_ipc_export(fluid_handle* h, int field_id, char out[64])
+int fluid_ipc_export(fluid_handle* h, int alloc_id, char out[64])
 {
-    if (int e = check_field(h, field_id, "fluid_ipc_export")) return e;
+    if (!h || !out) return FLUID_E_ARG;
+    if (alloc_id < 0 || alloc_id >= FLUID_IPC_COUNT)
+        return fl_fail(h, FLUID_E_ARG, "fluid_ipc_export: bad allocation id %d", alloc_id);
+    // a field id names the buffer the field lives in right now (the solver permutes them)
+    void* base = alloc_id == FLUID_IPC_SYNC ? (void*)h->d_sync
+               : alloc_id >= FLUID_IPC_SCRATCH0 ? (void*)(h->scratch[alloc_id - FLUID_IPC_SCRATCH0] - h->g.plane)
+               : (void*)(h->field[alloc_id] - h->g.plane);
     cudaIpcMemHandle_t mh;
-    FL_CUDA(h, cudaIpcGetMemHandle(&mh, h->field[field_id] - h->g.plane));
+    FL_CUDA(h, cudaIpcGetMemHandle(&mh, base));
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");
     memcpy(out, &mh, 64);
     return 0;
 }
 
-int fluid_ipc_import(fluid_handle* h, int peer_rank, int field_id, const char in[64])
+int fluid_ipc_import(fluid_handle* h, int peer_rank, int alloc_id, const char in[64])
 {
-    if (int e = check_field(h, field_id, "fluid_ipc_import")) return e;
+    if (!h || !in) return FLUID_E_ARG;
+    if (alloc_id < 0 || alloc_id >= FLUID_IPC_COUNT)
+        return fl_fail(h, FLUID_E_ARG, "fluid_ipc_import: bad allocation id %d", alloc_id);
     if (peer_rank < 0 || peer_rank >= h->nranks || peer_rank == h->rank)
         return fl_fail(h, FLUID_E_ARG, "fluid_ipc_import: bad peer rank %d", peer_rank);
     if (!h->comm) h->comm = new SlabComm();
@@ -92,7 +100,16 @@ int fluid_ipc_import(fluid_handle* h, int peer_rank, int field_id, const char in
     cudaIpcMemHandle_t mh; memcpy(&mh, in, 64);
     void* p = nullptr;
     FL_CUDA(h, cudaIpcOpenMemHandle(&p, mh, cudaIpcMemLazyEnablePeerAccess));
-    c->peer_alloc[peer_rank][field_id] = (float*)p;
+    // Imports happen at attach time, before any solve has permuted the buffers, and every rank
+    // permutes alike: the peer's buffer with id i keeps corresponding to this rank's alloc_base[i].
+    int slot = alloc_id;
+    if (alloc_id < FLUID_NFIELDS)
+        for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
+            if (h->alloc_base[i] == h->field[alloc_id] - h->g.plane) slot = i;
+    if (alloc_id >= FLUID_IPC_SCRATCH0 && alloc_id < FLUID_IPC_SYNC)
+        for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
+            if (h->alloc_base[i] == h->scratch[alloc_id - FLUID_IPC_SCRATCH0] - h->g.plane) slot = i;
+    c->peer_alloc[peer_rank][slot] = (float*)p;
     return 0;
 }
 

@@ -10,6 +10,7 @@
 #pragma once
 #include "handle.cuh"
 #include <nccl.h>
+#include <cuda.h>
 #include <dlfcn.h>
 
 struct SlabComm {
@@ -25,7 +26,12 @@ struct SlabComm {
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
-    float* peer_alloc[8][FLUID_NFIELDS] = {};              // IPC-mapped allocation bases (plane -1) of the other ranks
+    // IPC-mapped allocations of the other ranks, by allocation slot (fluid_handle::alloc_base order;
+    // [FLUID_IPC_SYNC] = the rank's flag block)
+    float* peer_alloc[8][FLUID_IPC_COUNT] = {};
+    // stream memory operation (driver entry point): the stream waits until *addr >= value
+    CUresult (*WaitValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned) = nullptr;
+    int push_state = 0;                                    // 0 = not probed yet, 1 = peer stores usable, -1 = NCCL only
 };
 
 static int comm_load(SlabComm* c, const char* path, std::string* err)
@@ -95,12 +101,150 @@ int fl_barrier(fluid_handle* h)
     return 0;
 }
 
+// ---- halo hand-over by peer stores ------------------------------------------------------------
+// rank r's mapping of the buffer that corresponds to this rank's `local` (plane 0), or nullptr
+static inline float* fl_peer_ptr(fluid_handle* h, int r, const float* local)
+{
+    SlabComm* c = (SlabComm*)h->comm;
+    if (!c) return nullptr;
+    for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
+        if (h->alloc_base[i] == local - h->g.plane)
+            return c->peer_alloc[r][i] ? c->peer_alloc[r][i] + h->g.plane : nullptr;
+    return nullptr;
+}
+
+// every buffer a sweep can write and the flag block are mapped from both z-neighbours, and the
+// driver offers stream waits on memory: sweeps hand their halos over by peer stores
+static inline bool fl_push_ready(fluid_handle* h);
+bool fl_push_usable(fluid_handle* h) { return fl_push_ready(h); }
+static inline bool fl_push_ready(fluid_handle* h)
+{
+    SlabComm* c = (SlabComm*)h->comm;
+    if (!c || h->nranks == 1) return false;
+    if (c->push_state == 0) {
+        c->push_state = -1;
+        const char* env = getenv("FLUID_SW_PUSH");
+        bool ok = !(env && atoi(env) == 0);
+        for (int side = 0; side < 2 && ok; ++side) {
+            const int r = side == 0 ? h->rank - 1 : h->rank + 1;
+            if (r < 0 || r >= h->nranks) continue;
+            for (int i = 0; i < FLUID_IPC_COUNT && ok; ++i) ok = c->peer_alloc[r][i] != nullptr;
+        }
+        if (ok) {
+            void* fn = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            ok = cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+                 q == cudaDriverEntryPointSuccess && fn;
+            if (ok) {
+                *(void**)(&c->WaitValue32) = fn;
+                // probe: a wait that is already satisfied (spare word of the flag block, 0 >= 0)
+                ok = c->WaitValue32((CUstream)h->stream, (CUdeviceptr)(h->d_sync + 8), 0u, CU_STREAM_WAIT_VALUE_GEQ) == CUDA_SUCCESS;
+            }
+        }
+        if (ok) c->push_state = 1;
+    }
+    return c->push_state == 1;
+}
+
+struct PushArgs {
+    const float4* src[6]; float4* dst[6];     // (field, side): two consecutive planes each
+    unsigned* flag[2];                        // the neighbours' arrival flags for this rank (nullptr = no neighbour)
+    unsigned* counter;
+    long long n4;                             // float4s per copy (2 planes)
+    int ncopy; unsigned seq;
+};
+
+// Stores this rank's boundary planes into the neighbours' halo planes over NVLink and, once every
+// CTA's stores are fenced, raises the neighbours' arrival flags to `seq`.
+__global__ void __launch_bounds__(128) k_push_halo(const PushArgs a)
+{
+    for (int c = 0; c < a.ncopy; ++c) {
+        const float4* __restrict__ s = a.src[c]; float4* __restrict__ d = a.dst[c];
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n4; i += (long long)gridDim.x * blockDim.x)
+            d[i] = s[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned done = atomicAdd(a.counter, 1u);
+        if (done == gridDim.x - 1) {                     // last CTA: all stores of all CTAs are fenced
+            *a.counter = 0;
+            __threadfence_system();
+            for (int sd = 0; sd < 2; ++sd)
+                if (a.flag[sd]) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.flag[sd]), "r"(a.seq) : "memory");
+        }
+    }
+}
+
+// hand the halo planes of `fields` (the buffers a sweep just wrote) to the z-neighbours; seq = this
+// sweep's number in h->halo_seq order
+int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stream, unsigned seq)
+{
+    SlabComm* c = (SlabComm*)h->comm;
+    const long long pl = h->g.plane;
+    PushArgs a = {};
+    a.n4 = 2 * pl / 4; a.seq = seq; a.counter = h->d_sync + 4;
+    for (int side = 0; side < 2; ++side) {
+        const int r = side == 0 ? h->rank - 1 : h->rank + 1;
+        if (r < 0 || r >= h->nranks) continue;
+        int zlo_r, dl_r; fl_slab_of(h->g.D, h->nranks, r, &zlo_r, &dl_r);
+        // my planes {1,2} -> lower neighbour's {Dl_r+1, Dl_r+2}; my {Dl-1,Dl} -> upper neighbour's {-1,0}.
+        // The neighbour's flag [1] is "raised by its upper neighbour", [0] "by its lower neighbour".
+        a.flag[side] = (unsigned*)c->peer_alloc[r][FLUID_IPC_SYNC] + (side == 0 ? 1 : 0);
+        for (int i = 0; i < n; ++i) {
+            float* peer = fl_peer_ptr(h, r, fields[i]);
+            if (!peer) return fl_fail(h, FLUID_E_COMM, "halo push: buffer of rank %d is not IPC-mapped", r);
+            a.src[a.ncopy] = (const float4*)(fields[i] + (side == 0 ? 1 : (long long)(h->g.Dl - 1)) * pl);
+            a.dst[a.ncopy] = (float4*)(peer + (side == 0 ? (long long)(dl_r + 1) : -1LL) * pl);
+            ++a.ncopy;
+        }
+    }
+    const int ctas = 16;                                  // 128 threads, no shared memory: fits beside a resident sweep CTA
+    k_push_halo<<<ctas, 128, 0, stream>>>(a);
+    FL_CHECK_LAUNCH(h);
+    return 0;
+}
+
+// where the fused sweep kernel writes: per face (0 lower, 1 upper) the neighbour's mapping of `fields`,
+// its arrival flag for this rank and the neighbour-local index of the first halo plane
+int fl_push_targets(fluid_handle* h, int n, float* const* fields, float* (*peer)[3], unsigned** flag, int* zdst)
+{
+    SlabComm* c = (SlabComm*)h->comm;
+    for (int side = 0; side < 2; ++side) {
+        flag[side] = nullptr; zdst[side] = 0;
+        for (int i = 0; i < 3; ++i) peer[side][i] = nullptr;
+        const int r = side == 0 ? h->rank - 1 : h->rank + 1;
+        if (r < 0 || r >= h->nranks) continue;
+        int zlo_r, dl_r; fl_slab_of(h->g.D, h->nranks, r, &zlo_r, &dl_r);
+        zdst[side] = side == 0 ? dl_r + 1 : -1;
+        flag[side] = (unsigned*)c->peer_alloc[r][FLUID_IPC_SYNC] + (side == 0 ? 1 : 0);
+        for (int i = 0; i < n; ++i) {
+            peer[side][i] = fl_peer_ptr(h, r, fields[i]);
+            if (!peer[side][i]) return fl_fail(h, FLUID_E_COMM, "fused sweep: buffer of rank %d is not IPC-mapped", r);
+        }
+    }
+    return 0;
+}
+
+// `stream` continues once both neighbours' halos of sweep `seq` have arrived
+int fl_halo_wait(fluid_handle* h, cudaStream_t stream, unsigned seq)
+{
+    SlabComm* c = (SlabComm*)h->comm;
+    for (int side = 0; side < 2; ++side) {
+        const int r = side == 0 ? h->rank - 1 : h->rank + 1;
+        if (r < 0 || r >= h->nranks) continue;
+        CUresult e = c->WaitValue32((CUstream)stream, (CUdeviceptr)(h->d_sync + side), seq, CU_STREAM_WAIT_VALUE_GEQ);
+        if (e != CUDA_SUCCESS) return fl_fail(h, FLUID_E_CUDA, "cuStreamWaitValue32 failed (%d)", (int)e);
+    }
+    return 0;
+}
+
 void fl_comm_release(fluid_handle* h)
 {
     SlabComm* c = (SlabComm*)h->comm;
     if (!c) return;
     for (int r = 0; r < 8; ++r)
-        for (int f = 0; f < FLUID_NFIELDS; ++f)
+        for (int f = 0; f < FLUID_IPC_COUNT; ++f)
             if (c->peer_alloc[r][f]) cudaIpcCloseMemHandle(c->peer_alloc[r][f]);
     if (c->comm && c->CommDestroy) c->CommDestroy(c->comm);
     cudaFree(c->d_token);
@@ -116,13 +260,13 @@ int fl_gather_sources(fluid_handle* h, int prev_id, GatherSrc* out)
         out->base[0] = h->field[prev_id]; out->zlo[0] = h->g.zlo; out->dl[0] = h->g.Dl;
         return 0;
     }
-    SlabComm* c = (SlabComm*)h->comm;
     for (int r = 0; r < h->nranks; ++r) {
         fl_slab_of(h->g.D, h->nranks, r, &out->zlo[r], &out->dl[r]);
         if (r == h->rank) { out->base[r] = h->field[prev_id]; continue; }
-        if (!c || !c->peer_alloc[r][prev_id])
+        float* peer = fl_peer_ptr(h, r, h->field[prev_id]);
+        if (!peer)
             return fl_fail(h, FLUID_E_COMM, "advect: field %d of rank %d is not IPC-mapped (fluid_ipc_import)", prev_id, r);
-        out->base[r] = c->peer_alloc[r][prev_id] + h->g.plane;
+        out->base[r] = peer;
     }
     return 0;
 }

@@ -36,11 +36,13 @@ static int alloc_all(fluid_handle* h)
     for (int i = 0; i < FLUID_NFIELDS; ++i) {
         FL_CUDA(h, cudaMalloc(&h->field[i], fbytes));
         FL_CUDA(h, cudaMemsetAsync(h->field[i], 0, fbytes, h->stream));   // simulation.cpp:38-43
+        h->alloc_base[i] = h->field[i];
         h->field[i] += h->g.plane;
     }
     for (int i = 0; i < 3; ++i) {
         FL_CUDA(h, cudaMalloc(&h->scratch[i], fbytes));
         FL_CUDA(h, cudaMemsetAsync(h->scratch[i], 0, fbytes, h->stream));
+        h->alloc_base[FLUID_NFIELDS + i] = h->scratch[i];
         h->scratch[i] += h->g.plane;
     }
     FL_CUDA(h, cudaMalloc(&h->cflags, (size_t)h->g.cells));
@@ -50,6 +52,8 @@ static int alloc_all(fluid_handle* h)
     h->n_partial = 148 * 8;
     FL_CUDA(h, cudaMalloc(&h->d_partial, (size_t)h->n_partial * FL_NSTAT * sizeof(double)));
     FL_CUDA(h, cudaMalloc(&h->d_out, FL_NSTAT * sizeof(double)));
+    FL_CUDA(h, cudaMalloc(&h->d_sync, 64 * sizeof(unsigned)));
+    FL_CUDA(h, cudaMemsetAsync(h->d_sync, 0, 64 * sizeof(unsigned), h->stream));
     return 0;
 }
 
@@ -150,7 +154,7 @@ void fluid_destroy(fluid_handle* h)
     for (int i = 0; i < 5; ++i) cudaFree(h->frame_staging[i]);
     if (h->cflags) cudaFree(h->cflags - h->g.plane);
     cudaFree(h->staging); cudaFree(h->d_partial); cudaFree(h->d_out);
-    cudaFree(h->d_xyz); cudaFree(h->d_val);
+    cudaFree(h->d_xyz); cudaFree(h->d_val); cudaFree(h->d_sync);
     for (auto& r : h->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     if (h->ev_frame_packed) cudaEventDestroy(h->ev_frame_packed);
@@ -186,6 +190,12 @@ int fluid_sync(fluid_handle* h)
 {
     if (!h) return FLUID_E_ARG;
     FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (h->nranks > 1 && h->halo_seq > 0) {              // fused halo hand-over: did an arrival wait time out?
+        unsigned err = 0;
+        FL_CUDA(h, cudaMemcpy(&err, h->d_sync + 16, sizeof err, cudaMemcpyDeviceToHost));
+        if (err) return fl_fail(h, FLUID_E_COMM, "z-neighbour %s never handed its halo planes over (arrival flag timed out)",
+                                err == 1 ? "below" : "above");
+    }
     return 0;
 }
 

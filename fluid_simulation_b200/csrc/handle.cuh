@@ -17,6 +17,11 @@ struct fluid_handle {
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     float* field[FLUID_NFIELDS] = {};
     float* scratch[3] = {};          // Jacobi ping-pong partners (up to 3 batched fields)
+    // Allocation starts (plane -1) in FLUID_IPC_* id order.  field[] / scratch[] are permuted by the
+    // solver's pointer swaps, identically on every rank; a buffer's id is found by its address.
+    float* alloc_base[FLUID_NFIELDS + 3] = {};
+    unsigned* d_sync = nullptr;      // [0] / [1] = arrival flags raised by the lower / upper z-neighbour, [2] = CTA counter
+    unsigned halo_seq = 0;           // sweeps whose halos went out through peer stores so far
     unsigned char* cflags = nullptr; // per-cell flag bytes, same pitched geometry as the fields
     bool flags_dirty = true;
     float* staging = nullptr;        // (Dl+2)*(H+2)*(W+2) floats, reference layout, for up/download

@@ -16,6 +16,11 @@ int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid, const 
 void fl_tiled_release(fluid_handle* h);                                  // tiled.cuh
 void fl_comm_release(fluid_handle* h);                                   // comm.cuh
 int fl_halo_exchange_on(fluid_handle* h, int n, float* const* fields, cudaStream_t stream);   // comm.cuh
+// comm.cuh: halo hand-over by peer stores + arrival flags (sweeps of the streaming kernel)
+bool fl_push_usable(fluid_handle* h);
+int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stream, unsigned seq);
+int fl_halo_wait(fluid_handle* h, cudaStream_t stream, unsigned seq);
+int fl_push_targets(fluid_handle* h, int n, float* const* fields, float* (*peer)[3], unsigned** flag, int* zdst);
 int fl_barrier(fluid_handle* h);                                         // comm.cuh
 
 static inline int fl_rebuild_flags(fluid_handle* h)

@@ -36,7 +36,9 @@
 #define SW_SMEM_MAX 232448               // 227 KB of dynamic shared memory per CTA on sm_100
 #define SW_SM_SMEM  233472               // 228 KB of shared memory per SM (each resident CTA also reserves 1 KB)
 
-struct SwSeg { int col, za, zb, down; };    // column (batched field * row tiles + row tile), planes za..zb, streamed downwards?
+// column (batched field * row tiles + row tile), planes za..zb; mode bit 0 = streamed downwards,
+// bits 1-2 = 1 + slab face (0 lower, 1 upper) whose two boundary planes this segment hands to the z-neighbour
+struct SwSeg { int col, za, zb, mode; };
 
 struct alignas(64) StreamArgs {
     CUtensorMap map[3];                  // source field of each batched solve (box SW_BOXW x BR x 1)
@@ -50,6 +52,16 @@ struct alignas(64) StreamArgs {
     float a, c_recip;
     int nty;                             // row tiles per field
     int flip;                            // 1 = this sweep streams every segment against its planned direction
+    // z-slabs, halos handed over inside the sweep (segments with a face in SwSeg.mode): the neighbour's
+    // mapping of dst[] per face, its arrival flag for this rank, this rank's per-face CTA counters
+    float* peer_dst[2][3];
+    unsigned* peer_flag[2];
+    unsigned* counter;
+    int peer_zdst[2];                    // neighbour-local index of the first of the two halo planes written
+    int n_edge;                          // edge segments per face (= columns)
+    unsigned seq;                        // value the flags are raised to
+    const unsigned* my_flag;             // this rank's arrival flags [face]; an edge segment starts once its face shows seq - 1
+    unsigned* err_word;                  // set when an arrival flag did not show up within SW_ARRIVAL_TIMEOUT_NS
     int dbg;                             // FLUID_SW_DBG timing experiments: 1 = no stores, 2 = no relaxation (results invalid)
 };
 
@@ -325,6 +337,64 @@ __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float*
     }
 }
 
+// An edge segment reads the z-neighbour's halo planes of the previous sweep and overwrites the
+// neighbour's halo planes of the sweep before that: both are safe once the neighbour's flag shows the
+// previous sweep (its edge CTAs of that face are done).  The flag is raised by a kernel on ANOTHER GPU
+// that does not depend on this launch; normally it was raised long ago.  The wait is bounded: a missing
+// neighbour becomes an error word the host reports (fluid_sync), not a hung GPU.
+#define SW_ARRIVAL_TIMEOUT_NS 20000000000ull
+__device__ __forceinline__ void sw_await_face(const StreamArgs& A, int side, int tid)
+{
+    if (tid == 0) {
+        const unsigned want = A.seq - 1u;
+        unsigned v;
+        unsigned long long t0 = 0;
+        for (unsigned spins = 0;; ++spins) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(A.my_flag + side) : "memory");
+            if ((int)(v - want) >= 0) break;
+            if ((spins & 1023u) == 1023u) {
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                if (t0 == 0) t0 = t;
+                else if (t - t0 > SW_ARRIVAL_TIMEOUT_NS) { atomicExch(A.err_word, 1u + (unsigned)side); break; }
+            }
+        }
+        asm volatile("fence.proxy.async;" ::: "memory");              // the halo planes are read by TMA
+    }
+    __syncthreads();
+}
+
+// An edge segment is done: copy the two boundary planes of this column (its owned rows; the first /
+// last row tile also takes the y ghost rows) into the z-neighbour's halo planes over NVLink, and let
+// the last CTA of the face raise the neighbour's arrival flag.
+template <int TY, int THREADS>
+__device__ __forceinline__ void sw_push_face(const StreamArgs& A, const Grid& g, const float* out, int batch, int tile,
+                                             int y0, int side, int tid)
+{
+    __syncthreads();                                                  // the CTA's stores are visible to the CTA
+    const int r0 = tile == 0 ? 0 : y0;
+    const int r1 = tile == A.nty - 1 ? g.rows - 1 : y0 + TY - 1;
+    const int n4 = (r1 - r0 + 1) * (g.pitch / 4);
+    const long long zsrc = side == 0 ? 1 : g.Dl - 1;
+#pragma unroll
+    for (int pl = 0; pl < 2; ++pl) {
+        const float4* __restrict__ s4 = reinterpret_cast<const float4*>(out + (zsrc + pl) * g.plane + (long long)r0 * g.pitch);
+        float4* __restrict__ d4 = reinterpret_cast<float4*>(A.peer_dst[side][batch] + ((long long)A.peer_zdst[side] + pl) * g.plane +
+                                                            (long long)r0 * g.pitch);
+        for (int i = tid; i < n4; i += THREADS) d4[i] = __ldcg(s4 + i);
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned done = atomicAdd(A.counter + side, 1u);
+        if (done == (unsigned)A.n_edge - 1u) {                        // every CTA of this face has fenced its stores
+            A.counter[side] = 0;
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(A.peer_flag[side]), "r"(A.seq) : "memory");
+        }
+    }
+}
+
 // One segment (planes za..zb of one column) streamed in direction DIR (+1 upwards in z, -1 downwards);
 // the TMA ring position and its mbarrier phase (s_iss, s_con, ph_con) run on from segment to segment.
 template <int TXW, int NP, int CPS, int MODE, int DIR>
@@ -352,6 +422,7 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     const int b = A.b[batch];
     const unsigned zmask4 = fl_zero_mask(b) * 0x01010101u;
     float* __restrict__ out = A.dst[batch];
+    if (sg.mode >> 1) sw_await_face(A, (sg.mode >> 1) - 1, tid);
 
     // plane p -> ring slot s_iss.  Every thread tracks the ring position, so that the slot and barrier
     // addresses stay warp-uniform; thread 0 alone arms the barrier and starts the copies.
@@ -427,6 +498,7 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     if (((g.zlo + ps) & 1) == 0) { for (;;) { SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
     else                         { for (;;) { SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
 #undef SW_STEP
+    if (sg.mode >> 1) sw_push_face<GE::TY, GE::THREADS>(A, g, out, batch, sg.col - batch * A.nty, y0, (sg.mode >> 1) - 1, tid);
 }
 
 // MODE 0 = Jacobi, 1 = red-black (colour 0 = (x+y+z) even first).  A CTA works through a short list
@@ -473,7 +545,7 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
 
     for (int si = A.seg_first[blockIdx.x]; si < A.seg_first[blockIdx.x + 1]; ++si) {
         const SwSeg sg = A.segs[si];
-        if ((sg.down ^ A.flip) & 1)
+        if ((sg.mode ^ A.flip) & 1)
             sw_segment<TXW, NP, CPS, MODE, -1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, x0, lane_in, exbits, safe);
         else
             sw_segment<TXW, NP, CPS, MODE, 1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, x0, lane_in, exbits, safe);
@@ -562,7 +634,11 @@ inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows
 #define SW_SEGCOST 4
 // part 0 = all planes 1..Dl.  A z-slab whose halo exchange is overlapped with the sweep splits them:
 // part 1 = the SW_EDGE planes next to each interior slab face (one CTA per column and face; they run
-// first, on the halo stream, and the exchange follows them), part 2 = the planes in between.
+// first, on the halo stream, and the exchange follows them), part 2 = the planes in between on the SMs
+// the edge CTAs leave free (NCCL's copy kernel needs SMs of its own once they are done), part 3 = the
+// planes in between on all SMs (halos handed over by peer stores: nothing else needs an SM), where the
+// CTAs that only start once an edge CTA has retired get that much less work; part 4 = parts 1 and 3 in
+// one grid, edge CTAs first, for the sweep that hands its halos over itself.
 #define SW_EDGE 8
 inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPlan* out)
 {
@@ -573,16 +649,21 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
         const Grid& g = h->g;
         const bool lo_face = h->rank > 0, hi_face = h->rank < h->nranks - 1;
         // planes zoff+1 .. zoff+Dl of every column are distributed (part 0: zoff = 0, Dl = g.Dl)
-        const int zoff = (part == 2 && lo_face) ? SW_EDGE : 0;
-        const int Dl = part == 2 ? g.Dl - zoff - (hi_face ? SW_EDGE : 0) : g.Dl;
+        const int zoff = (part >= 2 && lo_face) ? SW_EDGE : 0;
+        const int Dl = part >= 2 ? g.Dl - zoff - (hi_face ? SW_EDGE : 0) : g.Dl;
         const int nty = (g.H + ty - 1) / ty, ncol = nb * nty;
         const long long T = (long long)ncol * Dl;
         std::vector<SwSeg> segs; std::vector<int> first;
-        if (part == 1) {
+        if (part == 1 || part == 4) {
+            // part 4: the edge CTAs come first in the grid (they are dispatched first) and hand their
+            // boundary planes to the z-neighbour themselves; they stream towards the face
+            const int lo_mode = part == 4 ? (1 << 1) | 1 : 0, hi_mode = part == 4 ? (2 << 1) : 0;
             for (int c = 0; c < ncol; ++c) {
-                if (lo_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, 1, SW_EDGE, 0 }); }
-                if (hi_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, g.Dl - SW_EDGE + 1, g.Dl, 0 }); }
+                if (lo_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, 1, SW_EDGE, lo_mode }); }
+                if (hi_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, g.Dl - SW_EDGE + 1, g.Dl, hi_mode }); }
             }
+        }
+        if (part == 1) {
         } else
         if (s->zc_override > 0) {                        // tests: fixed chunk height, one CTA per segment
             const int zc = s->zc_override;
@@ -599,14 +680,18 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
             if (nc < h->sm_count / 2) nc = h->sm_count / 2;
             if (nc > T / 8) nc = T / 8;                  // tiny grids: at least 8 planes per CTA
             if (nc < 1) nc = 1;
+            // part 3: CTAs beyond the SMs the edge CTAs leave free start SW_EDGE + SW_SEGCOST steps late
+            const long long n_edge = (long long)ncol * ((lo_face ? 1 : 0) + (hi_face ? 1 : 0));
+            const long long n_prompt = (part >= 3 && n_edge < nc) ? nc - n_edge : nc;
+            const long long late = SW_EDGE + SW_SEGCOST;
             // Uniform plan: every column is cut into the same S ranges and one CTA streams range k of a
             // column, upwards for even k, downwards for odd k.  Neighbouring row tiles are then on the same
             // plane at the same time and the ranges of a column reach their shared boundary together, so
             // halo rows and halo planes are L2 hits instead of second HBM reads.  It leaves nc - S*ncol
             // SMs idle, which the HBM-bound kernel tolerates up to a point (plan_min_fill, per cent).
             const long long S = nc / ncol;
-            const bool uniform = s->plan_mode == 1 ||
-                (s->plan_mode == 0 && S >= 1 && S * ncol * 100 >= nc * s->plan_min_fill && Dl / (S > 0 ? S : 1) >= 3 * SW_MINSEG);
+            const bool uniform = part < 3 && (s->plan_mode == 1 ||
+                (s->plan_mode == 0 && S >= 1 && S * ncol * 100 >= nc * s->plan_min_fill && Dl / (S > 0 ? S : 1) >= 3 * SW_MINSEG));
             if (uniform && S >= 1 && Dl / S >= 1) {
                 for (long long k = 0; k < S; ++k)
                     for (int c = 0; c < ncol; ++c) {
@@ -621,7 +706,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
                 int c = 0, z = 0;
                 for (long long k = 0; k < nc; ++k) {
                     if (emit) first.push_back((int)segs.size());
-                    long long left = budget;
+                    long long left = budget - (k >= n_prompt ? late : 0);
                     while (c < ncol) {
                         const int rem = Dl - z;
                         long long take = left - SW_SEGCOST < rem ? left - SW_SEGCOST : rem;
@@ -667,12 +752,20 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     StreamState* s = sw_state(h);
     auto kern = jacobi ? k_sweep_stream<TXW, NP, CPS, 0> : k_sweep_stream<TXW, NP, CPS, 1>;
     FL_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
-    // z-slabs: the planes next to the slab faces are swept first on the halo stream and their exchange
-    // runs while the compute stream sweeps the planes in between
+    // z-slabs.  The planes next to the slab faces are swept by CTAs of their own, ahead of the planes in
+    // between, so that the halo hand-over overlaps the rest of the sweep.
+    //  * fused (default once the neighbours' buffers are IPC-mapped): one launch per sweep; the edge CTAs
+    //    store their boundary planes into the neighbour's halo over NVLink and raise its arrival flag, the
+    //    next sweep's launch waits on this rank's flags with a stream memory operation.  No second
+    //    stream, no communication kernel.
+    //  * NCCL: the edge CTAs run on the high-priority halo stream, ncclSend/ncclRecv follows them there.
+    // Slabs too thin for separate edge CTAs sweep whole columns and exchange afterwards.
     const bool overlap = h->nranks > 1 && s->overlap && s->zc_override == 0 && g.Dl >= 4 * SW_EDGE;
+    const bool push = h->nranks > 1 && fl_push_usable(h);
+    const bool fused = overlap && push;
     SwPlan plan, plan_edge;
-    if (int e = sw_get_plan(h, nb, GE::TY, CPS, overlap ? 2 : 0, &plan)) return e;
-    if (overlap) if (int e = sw_get_plan(h, nb, GE::TY, CPS, 1, &plan_edge)) return e;
+    if (int e = sw_get_plan(h, nb, GE::TY, CPS, fused ? 4 : overlap ? 2 : 0, &plan)) return e;
+    if (overlap && !fused) if (int e = sw_get_plan(h, nb, GE::TY, CPS, 1, &plan_edge)) return e;
     StreamArgs A;
     A.g = g; A.a = a; A.c_recip = 1.0f / c; A.flags = h->cflags;         // simulation.cpp:257
     A.nty = (g.H + GE::TY - 1) / GE::TY;
@@ -710,7 +803,12 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
             A.dst[i] = alt[i];
         }
         A.flip = (s->zigzag && (k & 1)) ? 1 : 0;         // odd sweeps stream the other way (L2 reuse)
-        if (overlap) {
+        const unsigned seq = push ? ++h->halo_seq : 0u;
+        if (fused) {
+            if (int e = fl_push_targets(h, nb, alt, A.peer_dst, A.peer_flag, A.peer_zdst)) return e;
+            A.counter = h->d_sync + 2; A.n_edge = nb * A.nty; A.seq = seq;
+            A.my_flag = h->d_sync; A.err_word = h->d_sync + 16;
+        } else if (overlap) {
             // ev_a = "the in-between planes of the previous sweep (or whatever preceded the solve) are done"
             if (k == 0) FL_CUDA(h, cudaEventRecord(h->ev_a, h->stream));
             FL_CUDA(h, cudaStreamWaitEvent(h->halo_stream, h->ev_a, 0));
@@ -721,15 +819,22 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         kern<<<plan.nctas, GE::THREADS, GE::SMEM, h->stream>>>(A);
         FL_CHECK_LAUNCH(h);
         for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
-        if (overlap) {
+        if (fused) {
+            // the next sweep's edge CTAs wait for the neighbours' halos themselves (sw_await_face);
+            // whatever follows the solve waits once, below
+        } else if (overlap) {
             if (int e = fl_halo_exchange_on(h, nb, cur, h->halo_stream)) return e;   // two planes each way
             FL_CUDA(h, cudaEventRecord(h->ev_b, h->halo_stream));
             FL_CUDA(h, cudaEventRecord(h->ev_a, h->stream));
             FL_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_b, 0));                  // next sweep sees the halos
+        } else if (push) {
+            if (int e = fl_halo_push(h, nb, cur, h->stream, seq)) return e;
+            if (int e = fl_halo_wait(h, h->stream, seq)) return e;
         } else if (h->nranks > 1) {
             if (int e = fl_halo_exchange(h, nb, cur)) return e;
         }
     }
+    if (fused && h->acc > 0) if (int e = fl_halo_wait(h, h->stream, h->halo_seq)) return e;
     if (pin) {
         cudaStreamAttrValue av = {};
         av.accessPolicyWindow.num_bytes = 0;

@@ -15,6 +15,7 @@ from .simulation import FIELDS, FluidError
 
 # the fields advect() gathers from: prev_field of each of the four calls (simulation.cpp:125-127, 136)
 GATHER_SOURCES = ("v_x_prev", "v_y_prev", "v_z_prev", "buffer")
+IPC_COUNT = len(FIELDS) + 4            # fields, 3 solver ping-pong partners, arrival-flag block (FLUID_IPC_COUNT)
 
 
 def nccl_library_path() -> str:
@@ -63,16 +64,20 @@ def attach(sim, dist, lib=None) -> None:
         uid = buf.raw
     uid = broadcast_bytes(dist, uid, 128)
     sim._ck(L.fluid_comm_init(sim._h, path, uid))
+    # CUDA IPC: the advection gather sources of every rank, and every solver buffer + the arrival flags of
+    # the two z-neighbours (sweeps then hand their halo planes over by peer stores, see include/fluid_cuda.h)
+    gather_ids = [FIELDS[name] for name in GATHER_SOURCES]
     mine = {}
-    for name in GATHER_SOURCES:
+    for aid in range(IPC_COUNT):
         buf = C.create_string_buffer(64)
-        sim._ck(L.fluid_ipc_export(sim._h, FIELDS[name], buf))
-        mine[name] = buf.raw
+        sim._ck(L.fluid_ipc_export(sim._h, aid, buf))
+        mine[aid] = buf.raw
     for r, handles in enumerate(all_gather_bytes(dist, mine)):
         if r == rank:
             continue
-        for name in GATHER_SOURCES:
-            sim._ck(L.fluid_ipc_import(sim._h, r, FIELDS[name], handles[name]))
+        wanted = range(IPC_COUNT) if abs(r - rank) == 1 else gather_ids
+        for aid in wanted:
+            sim._ck(L.fluid_ipc_import(sim._h, r, aid, handles[aid]))
     dist.barrier()
 
 

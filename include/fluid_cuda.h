@@ -162,9 +162,16 @@ int fluid_comm_unique_id(const char* nccl_lib_path, char out[128]);
 int fluid_comm_init(fluid_handle*, const char* nccl_lib_path, const char unique_id[128]);
 /* advect() gathers at arbitrary z (simulation.cpp:384-397): the gather sources v_x_prev, v_y_prev,
  * v_z_prev and buffer of every other rank are mapped through CUDA IPC (64-byte handles, exchanged by
- * the host program) and read over NVLink by the advection kernel. */
-int fluid_ipc_export(fluid_handle*, int field_id, char out[64]);
-int fluid_ipc_import(fluid_handle*, int peer_rank, int field_id, const char in[64]);
+ * the host program) and read over NVLink by the advection kernel.
+ * The linearSolver sweeps (simulation.cpp:258-272) hand their halo planes to the z-neighbours the same
+ * way once the neighbours' allocations are mapped: ids 0..FLUID_NFIELDS-1 are the fields,
+ * FLUID_IPC_SCRATCH0..+2 the solver's ping-pong partners and FLUID_IPC_SYNC the arrival flags.  With all
+ * of them imported from both neighbours a sweep ends in one small kernel that stores the two boundary
+ * planes straight into the neighbour's halo and raises its flag (the neighbour's streams wait on the
+ * flag with a stream memory operation); otherwise the exchange after a sweep is an ncclSend/ncclRecv. */
+enum { FLUID_IPC_SCRATCH0 = FLUID_NFIELDS, FLUID_IPC_SYNC = FLUID_NFIELDS + 3, FLUID_IPC_COUNT = FLUID_NFIELDS + 4 };
+int fluid_ipc_export(fluid_handle*, int alloc_id, char out[64]);
+int fluid_ipc_import(fluid_handle*, int peer_rank, int alloc_id, const char in[64]);
 /* device-side barrier across all ranks on the handle's stream (collective) */
 int fluid_barrier(fluid_handle*);
 
