@@ -5,8 +5,9 @@
 does, and fails loudly when the CUDA library or device is missing (there is no CPU path).
 """
 from .simulation import (Simulation, FluidError, FIELDS, FIELD_NAMES, SOLVER_RB, SOLVER_JACOBI,
-                         SOLVER_LEX, ELIDE_DEAD, NO_TILED, TILED_ALWAYS)
-from . import masks
+                         SOLVER_LEX, ELIDE_DEAD, NO_TILED, TILED_ALWAYS, VOX_HASHED, VOX_FIXED, VOX_CELLS)
+from . import masks, stl
 
 __all__ = ["Simulation", "FluidError", "FIELDS", "FIELD_NAMES", "SOLVER_RB", "SOLVER_JACOBI",
-           "SOLVER_LEX", "ELIDE_DEAD", "NO_TILED", "TILED_ALWAYS", "masks"]
+           "SOLVER_LEX", "ELIDE_DEAD", "NO_TILED", "TILED_ALWAYS", "VOX_HASHED", "VOX_FIXED", "VOX_CELLS",
+           "masks", "stl"]

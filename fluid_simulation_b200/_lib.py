@@ -27,6 +27,8 @@ SYMBOLS = {
     "fluid_download_field": (_i, [_p, _i, _p]),
     "fluid_upload_obstacles": (_i, [_p, _p]),
     "fluid_add_obstacles": (_i, [_p, _i, _p]),
+    "fluid_voxelize": (_i, [_p, _p, _i, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
+                            _i, C.POINTER(C.c_longlong)]),
     "fluid_add_density": (_i, [_p, _i, _p, _p]),
     "fluid_set_velocity": (_i, [_p, _i, _p, _p]),
     "fluid_step": (_i, [_p, _i]),

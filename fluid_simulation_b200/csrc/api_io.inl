@@ -94,6 +94,13 @@ int fluid_add_obstacles(fluid_handle* h, int n, const int* xyz)
     return 0;
 }
 
+int fluid_voxelize(fluid_handle* h, const float* tris, int n_tris, float scale, float rot_x, float rot_y,
+                   float rot_z, float tx, float ty, float tz, int sampling, long long* added)
+{
+    if (!h) return FLUID_E_ARG;
+    return fl_voxelize(h, tris, n_tris, scale, rot_x, rot_y, rot_z, tx, ty, tz, sampling, added);
+}
+
 int fluid_add_density(fluid_handle* h, int n, const int* xyz, const float* amount)
 {
     if (int e = check_xyz(h, n, xyz, "fluid_add_density")) return e;

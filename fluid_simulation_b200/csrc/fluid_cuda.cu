@@ -6,6 +6,7 @@
 #include "sweep_stream.cuh"
 #include "wavefront.cuh"
 #include "comm.cuh"
+#include "voxelize.cuh"
 #include <cstring>
 #include <new>
 

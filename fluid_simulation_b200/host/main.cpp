@@ -1,11 +1,13 @@
 // fluid_tunnel -- parametrised replacement of the reference's hard-coded main() (simulation.cpp:429-450):
 // builds a Simulation, installs an obstacle mask, runs `iter` steps, writes data/*.bin frames in the
 // reference's format and prints run()'s statistics plus the device time per step.
-//   fluid_tunnel [--w 128 --h 64 --d 64 --iter 100 --acc 15 --speed 30] [--obstacle none|sphere|box|FILE.bin]
+//   fluid_tunnel [--w 128 --h 64 --d 64 --iter 100 --acc 15 --speed 30] [--obstacle none|sphere|box|FILE.bin|FILE.stl]
+//                [--stl-scale 0.8 --stl-rot rx,ry,rz --stl-translate tx,ty,tz --stl-sampling hashed|fixed|cells]
 //                [--solver rb|jacobi|lex] [--elide] [--out data] [--dump-every 1] [--quiet]
 // FILE.bin = raw float32 padded mask (w+2)(h+2)(d+2) in the reference layout, e.g. dumped once from the
 // reference's STL loader (its output is not reproducible run to run).
 #include "simulation.h"
+#include "object_loader.h"
 #include "../../include/fluid_cuda.h"
 
 #include <cstdlib>
@@ -39,6 +41,9 @@ int main(int argc, char** argv)
     int w = 128, h = 64, d = 64, iter = 100, acc = 15, speed = 30, dump_every = 1;   // simulation.cpp:431-436
     std::string obstacle = "none", solver = "rb", out = "data";
     bool elide = false, quiet = false;
+    float stl_scale = 0.8f, stl_rot[3] = { 0, 0, 0 }, stl_tr[3] = { 0, 0, 0 };      // loadSTLIntoObstacles defaults
+    int stl_sampling = FLUID_VOX_HASHED;
+    auto triple = [](const char* s, float out[3]) { if (std::sscanf(s, "%f,%f,%f", out, out + 1, out + 2) != 3) { std::cerr << "expected a,b,c: " << s << "\n"; std::exit(2); } };
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
         auto val = [&]() -> const char* { if (i + 1 >= argc) { std::cerr << a << " needs a value\n"; std::exit(2); } return argv[++i]; };
@@ -48,6 +53,9 @@ int main(int argc, char** argv)
         else if (a == "--obstacle") obstacle = val(); else if (a == "--solver") solver = val();
         else if (a == "--out") out = val(); else if (a == "--dump-every") dump_every = std::atoi(val());
         else if (a == "--elide") elide = true; else if (a == "--quiet") quiet = true;
+        else if (a == "--stl-scale") stl_scale = (float)std::atof(val());
+        else if (a == "--stl-rot") triple(val(), stl_rot); else if (a == "--stl-translate") triple(val(), stl_tr);
+        else if (a == "--stl-sampling") { std::string m = val(); stl_sampling = m == "fixed" ? FLUID_VOX_FIXED : m == "cells" ? FLUID_VOX_CELLS : FLUID_VOX_HASHED; }
         else { std::cerr << "unknown argument " << a << "\n"; return 2; }
     }
     unsigned flags = solver == "jacobi" ? FLUID_SOLVER_JACOBI : solver == "lex" ? FLUID_SOLVER_LEX : FLUID_SOLVER_RB;
@@ -59,6 +67,9 @@ int main(int argc, char** argv)
         if (obstacle == "sphere" || obstacle == "box") {
             std::vector<float> m = analytic_mask(obstacle, w, h, d);
             sim.uploadObstacles(m.data());
+        } else if (obstacle.size() > 4 && (obstacle.compare(obstacle.size() - 4, 4, ".stl") == 0 || obstacle.compare(obstacle.size() - 4, 4, ".STL") == 0)) {
+            // the reference's main() route (simulation.cpp:441): voxelise a mesh, on the device
+            loadSTLIntoObstacles(obstacle.c_str(), sim, stl_sampling, stl_scale, stl_rot[0], stl_rot[1], stl_rot[2], stl_tr[0], stl_tr[1], stl_tr[2]);
         } else if (obstacle != "none") {
             std::vector<float> m((size_t)(w + 2) * (h + 2) * (d + 2));
             std::ifstream f(obstacle, std::ios::binary);

@@ -68,9 +68,8 @@ private:
     double ms_per_step_ = 0.0;
 };
 
-/* Load STL and populate obstacles: the reference's object_loader.cpp compiles unchanged against this
- * header (it only uses width/height/depth and addObstacle). */
-void loadSTLIntoObstacles(const char* stlFile, Simulation& sim, float scale, float rot_x, float rot_y,
-                          float rot_z, float translate_x, float translate_y, float translate_z);
+/* loadSTLIntoObstacles (the reference's object_loader.h) lives in object_loader.h: the mesh is voxelised on
+ * the device.  The reference's own object_loader.cpp also still compiles against this class (it only uses
+ * width / height / depth and addObstacle). */
 
 #endif

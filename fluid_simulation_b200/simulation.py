@@ -22,6 +22,7 @@ FIELDS = {
 FIELD_NAMES = list(FIELDS)
 
 SOLVER_RB, SOLVER_JACOBI, SOLVER_LEX = 0x0, 0x1, 0x2
+VOX_HASHED, VOX_FIXED, VOX_CELLS = 0, 1, 2          # fluid_voxelize sampling (include/fluid_cuda.h)
 ELIDE_DEAD, NO_TILED, TILED_ALWAYS = 0x10, 0x20, 0x40
 
 OP_SET_BOUNDS, OP_LIN_SOLVE, OP_DIFFUSE, OP_DIVERGENCE, OP_GRADIENT = 1, 2, 3, 4, 5
@@ -133,6 +134,31 @@ class Simulation:
     def addObstacles(self, xyz):
         xyz = np.ascontiguousarray(np.asarray(xyz, dtype=np.int32).reshape(-1, 3))
         self._ck(self._L.fluid_add_obstacles(self._h, len(xyz), xyz.ctypes.data))
+
+    # -- loadSTLIntoObstacles (object_loader.cpp:288-449) ------------------------------------
+    def voxelize(self, tris, scale=0.8, rot=(0.0, 0.0, 0.0), translate=(0.0, 0.0, 0.0), sampling=VOX_HASHED) -> int:
+        """Rotate / scale / place a triangle mesh ((n, 9) floats) and mark the cells inside it as obstacle,
+        on the device.  Returns the reference's "Added N obstacle points" count."""
+        tris = np.ascontiguousarray(np.asarray(tris, dtype=np.float32).reshape(-1, 9))
+        added = C.c_longlong(0)
+        self._ck(self._L.fluid_voxelize(self._h, tris.ctypes.data, len(tris), float(scale), float(rot[0]), float(rot[1]),
+                                        float(rot[2]), float(translate[0]), float(translate[1]), float(translate[2]),
+                                        int(sampling), C.byref(added)))
+        return int(added.value)
+
+    def load_stl(self, path, scale=0.8, rot=(0.0, 0.0, 0.0), translate=(0.0, 0.0, 0.0), sampling=VOX_HASHED) -> int:
+        """The reference's loadSTLIntoObstacles(path, sim, scale, rot_x, rot_y, rot_z, tx, ty, tz); an unreadable or
+        empty file is reported and skipped like the reference does (object_loader.cpp:292-296), returning 0."""
+        from .stl import read_stl
+        try:
+            tris = read_stl(path)
+        except OSError:
+            tris = np.zeros((0, 9), np.float32)
+        if len(tris) == 0:
+            import sys
+            print(f"Failed to load STL: {path}", file=sys.stderr)
+            return 0
+        return self.voxelize(tris, scale, rot, translate, sampling)
 
     def addDensity(self, x, y, z, amount):
         xyz = np.array([x, y, z], dtype=np.int32)

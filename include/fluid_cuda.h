@@ -105,6 +105,19 @@ int fluid_add_obstacles(fluid_handle*, int n, const int* xyz /* 3n */);
 int fluid_add_density(fluid_handle*, int n, const int* xyz /* 3n */, const float* amount /* n */);
 int fluid_set_velocity(fluid_handle*, int n, const int* xyz /* 3n */, const float* v /* 3n */);
 
+/* loadSTLIntoObstacles (object_loader.cpp:288-449) from the triangle list on: rotate the mesh about the
+ * reference's objCenter, build the 64^3 rejection grid, ray-parity test every lattice sample against every
+ * triangle and set obs = 1 in the simulation cells the inside samples map to; `added` receives the
+ * reference's "Added N obstacle points" count.  `tris` = n_tris x 9 host floats (v1, v2, v3 as read from
+ * the STL, object_loader.cpp:98-174).  The reference seeds its per-sample jitter and ray direction from
+ * the OpenMP thread id (:399), so its mask is not reproducible; `sampling` picks the replacement:
+ * HASHED = same distributions from a hash of the sample index, FIXED = no jitter and ray (1, 0.1, 0.2),
+ * CELLS = one sample per simulation cell instead of the 200^3 lattice (no porous masks).  Blocking. */
+enum { FLUID_VOX_HASHED = 0, FLUID_VOX_FIXED = 1, FLUID_VOX_CELLS = 2 };
+int fluid_voxelize(fluid_handle*, const float* tris, int n_tris, float scale, float rot_x, float rot_y,
+                   float rot_z, float translate_x, float translate_y, float translate_z, int sampling,
+                   long long* added);
+
 /* n x { inlet density, buffer = dens, step() } = the body of run()'s loop (simulation.cpp:65-71),
  * without the frame write.  Asynchronous. */
 int fluid_step(fluid_handle*, int n_steps);

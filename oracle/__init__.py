@@ -220,3 +220,34 @@ class OracleSim(_Base):
     def run_iterations(self, n=1): self.lib().fo_run_iterations(self.h, n)
     def diffuse_a(self): return self.lib().fo_diffuse_a(self.h)
     def project_h(self): return self.lib().fo_project_h(self.h)
+
+
+# ---- STL voxeliser checkers (object_loader.cpp:288-449) ---------------------------------------------
+class _VoSetup(C.Structure):
+    _fields_ = [("center", C.c_float * 3), ("max_radius", C.c_float), ("pmin", C.c_float * 3), ("pmax", C.c_float * 3),
+                ("obj_size", C.c_float), ("resolution", C.c_float), ("coarse_res", C.c_float), ("grid_scale", C.c_float),
+                ("nx", C.c_int), ("ny", C.c_int), ("nz", C.c_int)]
+
+
+def voxelize(tris, w, h, d, scale=0.8, rot=(0.0, 0.0, 0.0), translate=(0.0, 0.0, 0.0), mode=0):
+    """oracle/voxel_oracle.c: (padded obs mask (d+2, h+2, w+2) float32, added count, setup dict)."""
+    lib = OracleSim.lib()
+    lib.vo_voxelize.restype = C.c_longlong
+    lib.vo_voxelize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_float] * 7 + \
+                               [C.c_int, C.c_void_p, C.POINTER(_VoSetup)]
+    tris = np.ascontiguousarray(np.asarray(tris, dtype=np.float32).reshape(-1, 9))
+    obs = np.zeros((d + 2, h + 2, w + 2), np.float32)
+    st = _VoSetup()
+    added = lib.vo_voxelize(tris.ctypes.data, len(tris), w, h, d, scale, *[float(r) for r in rot],
+                            *[float(t) for t in translate], mode, obs.ctypes.data, C.byref(st))
+    setup = {k: (list(getattr(st, k)) if k in ("center", "pmin", "pmax") else getattr(st, k)) for k, _ in _VoSetup._fields_}
+    return obs, int(added), setup
+
+
+def ref_voxelize(path, w, h, d, scale=0.8, rot=(0.0, 0.0, 0.0), translate=(0.0, 0.0, 0.0), threads=None):
+    """The reference's own loadSTLIntoObstacles on a fresh Simulation: padded obs mask (not reproducible run to run)."""
+    if threads:
+        RefSim.set_threads(threads)
+    sim = RefSim(w, h, d)
+    sim.load_stl(path, scale, rot, translate)
+    return sim.get("obs").copy()
