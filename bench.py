@@ -119,7 +119,7 @@ def ncu_traffic():
 
 def workload(n_gpus, args):
     w, h = args.w or W0, args.h or H0
-    d = (args.d or D0) * n_gpus
+    d = (args.d or D0) * (1 if getattr(args, "strong", False) else n_gpus)     # --strong: --d is the whole tunnel
     return w, h, d, (args.acc or ACC0)
 
 
@@ -184,7 +184,7 @@ def run_reference_arm(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": mean_s * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "strong" if args.strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{w}x{h}x{d} tunnel, airfoil obstacle, acc={acc} (BASELINE.json configs[2])",
                    "parallelism": f"OpenMP x{best['cores']} on host cores",
                    "samples_executed": len(vals)},
@@ -294,9 +294,10 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong" if args.strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{w}x{h}x{d} tunnel, airfoil obstacle, acc={acc} "
-                                   f"(BASELINE.json configs[2]{' x' + str(world) + ' z-slabs' if world > 1 else ''})",
+                                   + ("(BASELINE.json configs[2]" + (f" x{world} z-slabs" if world > 1 else "") + ")"
+                                      if (w, h, acc, args.strong) == (W0, H0, ACC0, False) else "(custom size)"),
                        "solver": args.solver, "density_diffusion": "elided" if args.elide else "executed",
                        "parallelism": f"z-slab x{world}" if world > 1 else "1 GPU",
                        "l2": "state (11 fields, %.0f MB) exceeds the 126 MB L2" % (11 * 4 * local_cells / 1e6)},
@@ -357,7 +358,12 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--w", type=int); ap.add_argument("--h", type=int); ap.add_argument("--d", type=int)
     ap.add_argument("--acc", type=int)
+    ap.add_argument("--size", help="WxHxD, same as --w/--h/--d (whose short names torchrun's own parser trips over)")
+    ap.add_argument("--strong", action="store_true", help="--d is the depth of the whole tunnel, split over the GPUs "
+                    "(BASELINE.json configs[3], configs[4]); default: --d planes per GPU (weak scaling)")
     args = ap.parse_args()
+    if args.size:
+        args.w, args.h, args.d = (int(v) for v in args.size.lower().split("x"))
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3                                   # timing rule: W >= 3
     # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) are sent

@@ -364,14 +364,14 @@ __device__ __forceinline__ void sw_await_face(const StreamArgs& A, int side, int
     __syncthreads();
 }
 
-// An edge segment is done: copy the two boundary planes of this column (its owned rows; the first /
-// last row tile also takes the y ghost rows) into the z-neighbour's halo planes over NVLink, and let
-// the last CTA of the face raise the neighbour's arrival flag.
+// The two boundary planes of a face segment are final: copy this column's part of them (its owned rows;
+// the first / last row tile also takes the y ghost rows) into the z-neighbour's halo planes over NVLink.
+// Nothing waits for the stores here; sw_signal_face fences them when the segment is done.
 template <int TY, int THREADS>
 __device__ __forceinline__ void sw_push_face(const StreamArgs& A, const Grid& g, const float* out, int batch, int tile,
                                              int y0, int side, int tid)
 {
-    __syncthreads();                                                  // the CTA's stores are visible to the CTA
+    // (the __syncthreads that ended the previous step made the CTA's stores visible to the CTA)
     const int r0 = tile == 0 ? 0 : y0;
     const int r1 = tile == A.nty - 1 ? g.rows - 1 : y0 + TY - 1;
     const int n4 = (r1 - r0 + 1) * (g.pitch / 4);
@@ -383,6 +383,12 @@ __device__ __forceinline__ void sw_push_face(const StreamArgs& A, const Grid& g,
                                                             (long long)r0 * g.pitch);
         for (int i = tid; i < n4; i += THREADS) d4[i] = __ldcg(s4 + i);
     }
+}
+
+// The face segment is done: fence the hand-over stores (long since on their way) and let the last CTA of
+// the face raise the neighbour's arrival flag.
+__device__ __forceinline__ void sw_signal_face(const StreamArgs& A, int side, int tid)
+{
     __threadfence_system();
     __syncthreads();
     if (tid == 0) {
@@ -422,7 +428,7 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     const int b = A.b[batch];
     const unsigned zmask4 = fl_zero_mask(b) * 0x01010101u;
     float* __restrict__ out = A.dst[batch];
-    if (sg.mode >> 1) sw_await_face(A, (sg.mode >> 1) - 1, tid);
+    if ((sg.mode >> 1) && !(A.dbg & 4)) sw_await_face(A, (sg.mode >> 1) - 1, tid);     // dbg 4: timing experiment, results invalid
 
     // plane p -> ring slot s_iss.  Every thread tracks the ring position, so that the slot and barrier
     // addresses stay warp-uniform; thread 0 alone arms the barrier and starts the copies.
@@ -495,10 +501,15 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
         Up = Un; p += DIR; ++step; ++jc;                                                                \
         __syncthreads();                                                                                \
     }
-    if (((g.zlo + ps) & 1) == 0) { for (;;) { SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
-    else                         { for (;;) { SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
+    // A face segment streams away from its slab face: after four steps the two boundary planes are final
+    // and go to the z-neighbour while the rest of the segment is still being swept.
+    const int face = (sg.mode >> 1) - 1;
+#define SW_HAND_OVER if (face >= 0 && step == 4 && !(A.dbg & 8)) sw_push_face<GE::TY, GE::THREADS>(A, g, out, batch, sg.col - batch * A.nty, y0, face, tid);
+    if (((g.zlo + ps) & 1) == 0) { for (;;) { SW_HAND_OVER SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
+    else                         { for (;;) { SW_HAND_OVER SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
 #undef SW_STEP
-    if (sg.mode >> 1) sw_push_face<GE::TY, GE::THREADS>(A, g, out, batch, sg.col - batch * A.nty, y0, (sg.mode >> 1) - 1, tid);
+#undef SW_HAND_OVER
+    if (face >= 0 && !(A.dbg & 8)) sw_signal_face(A, face, tid);
 }
 
 // MODE 0 = Jacobi, 1 = red-black (colour 0 = (x+y+z) even first).  A CTA works through a short list
@@ -545,7 +556,10 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
 
     for (int si = A.seg_first[blockIdx.x]; si < A.seg_first[blockIdx.x + 1]; ++si) {
         const SwSeg sg = A.segs[si];
-        if ((sg.mode ^ A.flip) & 1)
+        // face segments always stream away from their face (lower face: upwards), the others as planned,
+        // reversed on odd sweeps
+        const bool down = (sg.mode >> 1) ? (sg.mode >> 1) == 2 : (((sg.mode ^ A.flip) & 1) != 0);
+        if (down)
             sw_segment<TXW, NP, CPS, MODE, -1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, x0, lane_in, exbits, safe);
         else
             sw_segment<TXW, NP, CPS, MODE, 1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, x0, lane_in, exbits, safe);
@@ -563,6 +577,7 @@ struct SwPlan {                            // segment table of one (fields, row 
     SwSeg* segs = nullptr; int* seg_first = nullptr; int nctas = 0;
 };
 
+#define SW_EDGE_DEFAULT 8
 struct StreamState {
     sw_encode_fn encode = nullptr;
     std::map<std::pair<const float*, int>, CUtensorMap> maps;   // (field buffer, box rows * 1024 + box width) -> 3-D tensor map
@@ -570,6 +585,8 @@ struct StreamState {
     int zc_override = 0;
     bool zigzag = true, unbatch = false, overlap = true;
     int cfg = 0, dbg = 0;
+    bool face_cta = true;                                       // separate edge CTAs (plan part 4); FLUID_SW_FACE_CTA=0: hand-over inside ordinary segments (part 5)
+    int edge = SW_EDGE_DEFAULT;                                 // planes per edge segment at an interior slab face (>= 2)
     int plan_mode = 2, plan_min_fill = 85;                      // FLUID_SW_PLAN: 0 = auto, 1 = uniform ranges, 2 = balanced budget
 };
 
@@ -588,6 +605,8 @@ inline StreamState* sw_state(fluid_handle* h)
         if (const char* e = getenv("FLUID_SW_OVERLAP")) s->overlap = atoi(e) != 0;
         if (const char* e = getenv("FLUID_SW_CFG")) s->cfg = atoi(e);
         if (const char* e = getenv("FLUID_SW_DBG")) s->dbg = atoi(e);
+        if (const char* e = getenv("FLUID_SW_EDGE")) { s->edge = atoi(e); if (s->edge < 2) s->edge = 2; }
+        if (const char* e = getenv("FLUID_SW_FACE_CTA")) s->face_cta = atoi(e) != 0;
         if (const char* e = getenv("FLUID_SW_PLAN")) s->plan_mode = atoi(e);
         if (const char* e = getenv("FLUID_SW_PLAN_FILL")) s->plan_min_fill = atoi(e);
         h->tiled = s;
@@ -633,13 +652,14 @@ inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows
 #define SW_MINSEG 5
 #define SW_SEGCOST 4
 // part 0 = all planes 1..Dl.  A z-slab whose halo exchange is overlapped with the sweep splits them:
-// part 1 = the SW_EDGE planes next to each interior slab face (one CTA per column and face; they run
+// part 1 = the `edge` planes next to each interior slab face (one CTA per column and face; they run
 // first, on the halo stream, and the exchange follows them), part 2 = the planes in between on the SMs
 // the edge CTAs leave free (NCCL's copy kernel needs SMs of its own once they are done), part 3 = the
 // planes in between on all SMs (halos handed over by peer stores: nothing else needs an SM), where the
 // CTAs that only start once an edge CTA has retired get that much less work; part 4 = parts 1 and 3 in
-// one grid, edge CTAs first, for the sweep that hands its halos over itself.
-#define SW_EDGE 8
+// one grid, edge CTAs first, for the sweep that hands its halos over itself; part 5 = all planes as in
+// part 0, the segments that touch a slab face doing the hand-over on their way (FLUID_SW_FACE_CTA=0; as fast
+// with one face per rank, slower with two: 4 GPUs 30.2 vs 27.9 ms/step).
 inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPlan* out)
 {
     StreamState* s = sw_state(h);
@@ -649,18 +669,19 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
         const Grid& g = h->g;
         const bool lo_face = h->rank > 0, hi_face = h->rank < h->nranks - 1;
         // planes zoff+1 .. zoff+Dl of every column are distributed (part 0: zoff = 0, Dl = g.Dl)
-        const int zoff = (part >= 2 && lo_face) ? SW_EDGE : 0;
-        const int Dl = part >= 2 ? g.Dl - zoff - (hi_face ? SW_EDGE : 0) : g.Dl;
+        const bool split = part >= 2 && part <= 4;          // edge planes have CTAs of their own
+        const int zoff = (split && lo_face) ? s->edge : 0;
+        const int Dl = split ? g.Dl - zoff - (hi_face ? s->edge : 0) : g.Dl;
         const int nty = (g.H + ty - 1) / ty, ncol = nb * nty;
         const long long T = (long long)ncol * Dl;
         std::vector<SwSeg> segs; std::vector<int> first;
         if (part == 1 || part == 4) {
             // part 4: the edge CTAs come first in the grid (they are dispatched first) and hand their
-            // boundary planes to the z-neighbour themselves; they stream towards the face
-            const int lo_mode = part == 4 ? (1 << 1) | 1 : 0, hi_mode = part == 4 ? (2 << 1) : 0;
+            // boundary planes to the z-neighbour themselves; they stream away from the face
+            const int lo_mode = part == 4 ? (1 << 1) : 0, hi_mode = part == 4 ? (2 << 1) | 1 : 0;
             for (int c = 0; c < ncol; ++c) {
-                if (lo_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, 1, SW_EDGE, lo_mode }); }
-                if (hi_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, g.Dl - SW_EDGE + 1, g.Dl, hi_mode }); }
+                if (lo_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, 1, s->edge, lo_mode }); }
+                if (hi_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, g.Dl - s->edge + 1, g.Dl, hi_mode }); }
             }
         }
         if (part == 1) {
@@ -680,10 +701,12 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
             if (nc < h->sm_count / 2) nc = h->sm_count / 2;
             if (nc > T / 8) nc = T / 8;                  // tiny grids: at least 8 planes per CTA
             if (nc < 1) nc = 1;
-            // part 3: CTAs beyond the SMs the edge CTAs leave free start SW_EDGE + SW_SEGCOST steps late
+            // parts 3 / 4: the edge CTAs are dispatched first, in waves of nc; an in-between CTA starts when a
+            // slot frees up, so the last n_edge % nc of them start one edge segment (+ its pipeline fill) later
+            // than the others and get that much less work
             const long long n_edge = (long long)ncol * ((lo_face ? 1 : 0) + (hi_face ? 1 : 0));
-            const long long n_prompt = (part >= 3 && n_edge < nc) ? nc - n_edge : nc;
-            const long long late = SW_EDGE + SW_SEGCOST;
+            const long long n_prompt = (part == 3 || part == 4) ? nc - n_edge % nc : nc;
+            const long long late = s->edge + SW_SEGCOST + 2;
             // Uniform plan: every column is cut into the same S ranges and one CTA streams range k of a
             // column, upwards for even k, downwards for odd k.  Neighbouring row tiles are then on the same
             // plane at the same time and the ranges of a column reach their shared boundary together, so
@@ -730,6 +753,39 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
             }
         }
         first.push_back((int)segs.size());
+        if (part == 5) {
+            // Hand-over inside ordinary segments: the first segment of a column (za = 1) takes the lower face,
+            // the last (zb = Dl) the upper face; a segment that spans a whole column with two faces is cut
+            // in the middle.  Face segments go first in their CTA, so the flags rise early in the sweep.
+            std::vector<SwSeg> s2; std::vector<int> f2;
+            bool ok = true;
+            for (size_t k = 0; k + 1 < first.size(); ++k) {
+                std::vector<SwSeg> mine, faces, rest;
+                for (int i = first[k]; i < first[k + 1]; ++i) {
+                    SwSeg sg = segs[i];
+                    const bool lo = lo_face && sg.za == 1, hi = hi_face && sg.zb == g.Dl;
+                    if (lo && hi) {
+                        const int m = (sg.za + sg.zb) / 2;
+                        mine.push_back(SwSeg{ sg.col, sg.za, m, 1 << 1 });
+                        mine.push_back(SwSeg{ sg.col, m + 1, sg.zb, (2 << 1) | 1 });
+                    } else {
+                        if (lo) sg.mode = 1 << 1;
+                        if (hi) sg.mode = (2 << 1) | 1;
+                        mine.push_back(sg);
+                    }
+                }
+                for (const SwSeg& sg : mine) {
+                    if ((sg.mode >> 1) && sg.zb - sg.za + 1 < 2) ok = false;      // two planes to hand over
+                    ((sg.mode >> 1) ? faces : rest).push_back(sg);
+                }
+                f2.push_back((int)s2.size());
+                s2.insert(s2.end(), faces.begin(), faces.end());
+                s2.insert(s2.end(), rest.begin(), rest.end());
+            }
+            f2.push_back((int)s2.size());
+            if (!ok) return sw_get_plan(h, nb, ty, cps, 4, out);                   // degenerate cut: separate edge CTAs
+            segs.swap(s2); first.swap(f2);
+        }
         SwPlan pl;
         pl.nctas = (int)first.size() - 1;
         FL_CUDA(h, cudaMalloc(&pl.segs, segs.size() * sizeof(SwSeg)));
@@ -760,11 +816,11 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     //    stream, no communication kernel.
     //  * NCCL: the edge CTAs run on the high-priority halo stream, ncclSend/ncclRecv follows them there.
     // Slabs too thin for separate edge CTAs sweep whole columns and exchange afterwards.
-    const bool overlap = h->nranks > 1 && s->overlap && s->zc_override == 0 && g.Dl >= 4 * SW_EDGE;
+    const bool overlap = h->nranks > 1 && s->overlap && s->zc_override == 0 && g.Dl >= 4 * s->edge;
     const bool push = h->nranks > 1 && fl_push_usable(h);
     const bool fused = overlap && push;
     SwPlan plan, plan_edge;
-    if (int e = sw_get_plan(h, nb, GE::TY, CPS, fused ? 4 : overlap ? 2 : 0, &plan)) return e;
+    if (int e = sw_get_plan(h, nb, GE::TY, CPS, fused ? (s->face_cta ? 4 : 5) : overlap ? 2 : 0, &plan)) return e;
     if (overlap && !fused) if (int e = sw_get_plan(h, nb, GE::TY, CPS, 1, &plan_edge)) return e;
     StreamArgs A;
     A.g = g; A.a = a; A.c_recip = 1.0f / c; A.flags = h->cflags;         // simulation.cpp:257

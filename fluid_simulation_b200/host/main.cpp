@@ -2,7 +2,7 @@
 // builds a Simulation, installs an obstacle mask, runs `iter` steps, writes data/*.bin frames in the
 // reference's format and prints run()'s statistics plus the device time per step.
 //   fluid_tunnel [--w 128 --h 64 --d 64 --iter 100 --acc 15 --speed 30] [--obstacle none|sphere|box|FILE.bin|FILE.stl]
-//                [--stl-scale 0.8 --stl-rot rx,ry,rz --stl-translate tx,ty,tz --stl-sampling hashed|fixed|cells]
+//                [--restart DIR[:FRAME]] [--stl-scale 0.8 --stl-rot rx,ry,rz --stl-translate tx,ty,tz --stl-sampling hashed|fixed|cells]
 //                [--solver rb|jacobi|lex] [--elide] [--out data] [--dump-every 1] [--quiet]
 // FILE.bin = raw float32 padded mask (w+2)(h+2)(d+2) in the reference layout, e.g. dumped once from the
 // reference's STL loader (its output is not reproducible run to run).
@@ -39,7 +39,7 @@ static std::vector<float> analytic_mask(const std::string& kind, int w, int h, i
 int main(int argc, char** argv)
 {
     int w = 128, h = 64, d = 64, iter = 100, acc = 15, speed = 30, dump_every = 1;   // simulation.cpp:431-436
-    std::string obstacle = "none", solver = "rb", out = "data";
+    std::string obstacle = "none", solver = "rb", out = "data", restart;
     bool elide = false, quiet = false;
     float stl_scale = 0.8f, stl_rot[3] = { 0, 0, 0 }, stl_tr[3] = { 0, 0, 0 };      // loadSTLIntoObstacles defaults
     int stl_sampling = FLUID_VOX_HASHED;
@@ -53,6 +53,7 @@ int main(int argc, char** argv)
         else if (a == "--obstacle") obstacle = val(); else if (a == "--solver") solver = val();
         else if (a == "--out") out = val(); else if (a == "--dump-every") dump_every = std::atoi(val());
         else if (a == "--elide") elide = true; else if (a == "--quiet") quiet = true;
+        else if (a == "--restart") restart = val();
         else if (a == "--stl-scale") stl_scale = (float)std::atof(val());
         else if (a == "--stl-rot") triple(val(), stl_rot); else if (a == "--stl-translate") triple(val(), stl_tr);
         else if (a == "--stl-sampling") { std::string m = val(); stl_sampling = m == "fixed" ? FLUID_VOX_FIXED : m == "cells" ? FLUID_VOX_CELLS : FLUID_VOX_HASHED; }
@@ -76,6 +77,12 @@ int main(int argc, char** argv)
             if (!f.read((char*)m.data(), (std::streamsize)(m.size() * sizeof(float))))
                 throw std::runtime_error("cannot read obstacle mask " + obstacle);
             sim.uploadObstacles(m.data());
+        }
+        if (!restart.empty()) {                      // DIR or DIR:FRAME; the frame's obs replaces --obstacle
+            const size_t c = restart.rfind(':');
+            const long k = sim.restartFromFrames(c == std::string::npos ? restart : restart.substr(0, c),
+                                                 c == std::string::npos ? -1 : std::atol(restart.c_str() + c + 1));
+            if (!quiet) std::cout << "restarted from frame " << k << "\n";
         }
         sim.run();
         if (!quiet) {

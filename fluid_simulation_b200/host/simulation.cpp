@@ -75,6 +75,37 @@ void Simulation::downloadField(int field_id, float* padded_host)
     check(fluid_download_field(h_, field_id, padded_host), "downloadField");
 }
 
+long Simulation::restartFromFrames(const std::string& dir, long frame)
+{
+    // a dumped frame holds dens, obs and v; the other six fields are scratch that step() overwrites before
+    // reading them (simulation.cpp:96-150), so nothing else is needed
+    static const char* names[5] = { "data.bin", "obs.bin", "v_x.bin", "v_y.bin", "v_z.bin" };
+    static const int ids[5] = { FLUID_DENS, FLUID_OBS, FLUID_VX, FLUID_VY, FLUID_VZ };
+    const size_t npad = (size_t)(width + 2) * (height + 2) * (depth + 2);
+    std::vector<float> buf(npad);
+    long frames = -1;
+    std::FILE* fs[5] = {};
+    auto close_all = [&]() { for (auto& f : fs) if (f) { std::fclose(f); f = nullptr; } };
+    for (int i = 0; i < 5; ++i) {
+        fs[i] = std::fopen((dir + "/" + names[i]).c_str(), "rb");
+        if (!fs[i]) { close_all(); throw std::runtime_error("restart: cannot open " + dir + "/" + names[i]); }
+        std::fseek(fs[i], 0, SEEK_END);
+        const long n = (long)((size_t)std::ftell(fs[i]) / (npad * sizeof(float)));
+        frames = frames < 0 || n < frames ? n : frames;
+    }
+    const long k = frame >= 0 ? frame : frames + frame;
+    if (frames < 1 || k < 0 || k >= frames) { close_all(); throw std::runtime_error("restart: frame out of range in " + dir); }
+    flush();
+    for (int i = 0; i < 5; ++i) {
+        std::fseek(fs[i], (long)((size_t)k * npad * sizeof(float)), SEEK_SET);
+        if (std::fread(buf.data(), sizeof(float), npad, fs[i]) != npad) { close_all(); throw std::runtime_error("restart: short read"); }
+        if (ids[i] == FLUID_OBS) check(fluid_upload_obstacles(h_, buf.data()), "restart obs");
+        else check(fluid_upload_field(h_, ids[i], buf.data()), "restart field");
+    }
+    close_all();
+    return k;
+}
+
 void Simulation::statistics(double out[9])
 {
     flush();
@@ -133,7 +164,18 @@ void Simulation::run()
     check(fluid_timer_stop(h_, &ms), "timer");
     ms_per_step_ = iter > 0 ? ms / iter : 0.0;
     write_pending_frame();
+    const bool wrote = files_[0] != nullptr;
     for (auto& f : files_) if (f) { std::fclose(f); f = nullptr; }
+    if (wrote) {
+        // what the reference's viewers keep in hand-synchronised constants (GUI/config.py:8-11, gui.py:32-34)
+        if (std::FILE* m = std::fopen((out_dir_ + "/meta.json").c_str(), "w")) {
+            std::fprintf(m, "{\n \"width\": %d, \"height\": %d, \"depth\": %d, \"padded\": [%d, %d, %d],\n \"frames\": %d, \"dump_every\": %d,"
+                            " \"dtype\": \"float32\", \"order\": \"z,y,x (C order, padded)\",\n \"files\": [\"data.bin\", \"obs.bin\", \"v_x.bin\", \"v_y.bin\", \"v_z.bin\"],\n"
+                            " \"speed\": %d, \"dt\": %.9g, \"diff\": %.9g, \"visc\": %.9g, \"acc\": %d\n}\n",
+                         width, height, depth, depth + 2, height + 2, width + 2, iter / dump_every, dump_every, speed, dt, diff, visc, acc);
+            std::fclose(m);
+        }
+    }
     double st[9]; statistics(st);
     if (!quiet) {                                                                             // :81-90
         std::cout << "\n--- statistics -------------------------------------------------\n";

@@ -60,6 +60,9 @@ public:
     void setOutputDirectory(const std::string& dir) { out_dir_ = dir; }
     void uploadObstacles(const float* obs_padded);                            // whole mask at once
     void downloadField(int field_id, float* padded_host);
+    /* restart: load frame `frame` (negative = from the end) of dir/{data,obs,v_x,v_y,v_z}.bin as
+     * the current state; the following steps reproduce the original run bit for bit.  Returns the frame index. */
+    long restartFromFrames(const std::string& dir, long frame = -1);
     void statistics(double out[9]);
     double msPerStepLastRun() const { return ms_per_step_; }
     fluid_handle* handle() { flush(); return h_; }

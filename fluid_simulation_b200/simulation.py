@@ -280,6 +280,35 @@ class Simulation:
                 f.write(arr.tobytes())
             self._frame_pending = False
 
+    # -- restart: a dumped frame is a complete state ----------------------------
+    def write_sidecar(self, directory, frames, dump_every=1):
+        """data/meta.json: what the reference's viewers keep in hand-synchronised constants
+        (GUI/config.py:8-11, gui.py:32-34) and what a restart needs."""
+        import json
+        meta = {"width": self.width, "height": self.height, "depth": self.depth, "padded": [self.depth + 2, self.height + 2, self.width + 2],
+                "frames": int(frames), "dump_every": int(dump_every), "dtype": "float32", "order": "z,y,x (C order, padded)",
+                "files": list(FRAME_FILES), "speed": self.speed, "dt": self.dt, "diff": self.diff, "visc": self.visc, "acc": self.acc}
+        with open(os.path.join(directory, "meta.json"), "w") as f:
+            json.dump(meta, f, indent=1)
+
+    def restart_from_frames(self, directory="data", frame=-1):
+        """Load frame `frame` (negative = from the end) of data/{data,obs,v_x,v_y,v_z}.bin as the current
+        state.  The other six fields are scratch that step() overwrites before reading (v_*_prev and buffer
+        are copied from v / dens, pressure and divergence are recomputed, simulation.cpp:96-150), so the
+        steps that follow reproduce the original run bit for bit.  Returns the frame index loaded."""
+        npad = (self.depth + 2) * (self.height + 2) * (self.width + 2)
+        sizes = [os.path.getsize(os.path.join(directory, n)) for n in FRAME_FILES]
+        frames = min(sizes) // (4 * npad)
+        if frames < 1 or any(sz % (4 * npad) for sz in sizes):
+            raise FluidError(f"{directory}: frame files do not hold whole {self.width}x{self.height}x{self.depth} frames")
+        k = frame if frame >= 0 else frames + frame
+        if not 0 <= k < frames:
+            raise FluidError(f"{directory}: frame {frame} out of range (0..{frames - 1})")
+        for name, field in zip(FRAME_FILES, ("dens", "obs", "v_x", "v_y", "v_z")):
+            a = np.fromfile(os.path.join(directory, name), dtype=np.float32, count=npad, offset=4 * npad * k)
+            self.set(field, a.reshape(self.depth + 2, self.height + 2, self.width + 2))
+        return k
+
     def run(self, directory="data", dump_every=1, verbose=True):
         """Simulation::run() (simulation.cpp:49-91): `iter` steps, frames appended to data/*.bin,
         density sum every 100 steps and the final min/max statistics on stdout."""
@@ -297,6 +326,10 @@ class Simulation:
             if verbose and (i + 1) % 100 == 0 and i > 0:
                 print(f"step {i + 1}\n  density sum = {self.stats()['dens_sum']:g}")
         self.flush_frames()
+        if directory is not None:
+            for f in self._frame_files:
+                f.flush()
+            self.write_sidecar(directory, self.iter // dump_every, dump_every)
         st = self.stats()
         if verbose:
             print("\n--- statistics -------------------------------------------------")

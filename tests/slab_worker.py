@@ -35,10 +35,13 @@ def main():
 
     failures = 0
     cases = [("rb", SOLVER_RB, ORDER_RB), ("jacobi", SOLVER_JACOBI, ORDER_JACOBI)]
-    shapes = [(24, 16, 12), (128, 30, 17), (130, 9, 9), (256, 40, 4 * world + 3), (132, 20, 35 * world + 1)]
+    # thin slabs (whole-column sweeps + hand-over kernel), thick ragged slabs (edge CTAs hand the halos over
+    # inside the sweep), odd sweep counts (the solver's buffers end up permuted, on every rank alike), and the
+    # 4- and 8-warp-column kernel configurations (W > 256, W > 512)
+    shapes = [(24, 16, 12, 4), (128, 30, 17, 4), (130, 9, 9, 4), (256, 40, 4 * world + 3, 4), (132, 20, 35 * world + 1, 4),
+              (132, 18, 33 * world, 3), (260, 12, 33 * world + 2, 3), (516, 6, 32 * world, 4)]
     for name, flag, order in cases:
-        for (w, h, d) in shapes:
-            acc = 4
+        for (w, h, d, acc) in shapes:
             st = masks.random_state(w, h, d, seed=11)
             gpu = Simulation(w, h, d, 1, acc=acc, flags=flag, rank=rank, nranks=world)
             multi_gpu.attach(gpu, dist)
