@@ -236,14 +236,16 @@ def run_ours(args):
 
     # ---- device-resident timing ------------------------------------------------------------
     sim.run_iterations(args.warmup)
-    barrier()
+    # everything slow (NVML start-up is tens of ms) happens BEFORE the barrier: a rank that enters the timed
+    # region late keeps its z-neighbours waiting, and the reported time is the maximum over the ranks
     vis = [v.strip() for v in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if v.strip()]
     entry = vis[local] if local < len(vis) else str(local)          # NVML numbers physical devices
     sampler = (ClockSampler(int(entry)) if entry.isdigit() else ClockSampler(local, entry[4:] if entry.startswith("GPU-") else None)) \
         if rank == 0 else None
+    sim.profile(True); sim.profile_read()
+    barrier()
     if sampler:
         sampler.start()
-    sim.profile(True); sim.profile_read()
     l0 = sim.launch_count()
     sim.timer_start()
     sim.run_iterations(args.steps)
