@@ -101,6 +101,25 @@ int fluid_voxelize(fluid_handle* h, const float* tris, int n_tris, float scale, 
     return fl_voxelize(h, tris, n_tris, scale, rot_x, rot_y, rot_z, tx, ty, tz, sampling, added);
 }
 
+int fluid_render_slice(fluid_handle* h, int field_id, int z, double vmin, double vmax, double obstacle_alpha,
+                       unsigned char* rgb_host)
+{
+    return fl_render_slice(h, field_id, z, vmin, vmax, obstacle_alpha, rgb_host);
+}
+
+int fluid_density_cmap(double lut[768])
+{
+    if (!lut) return FLUID_E_ARG;
+    pp_density_cmap(reinterpret_cast<double(*)[3]>(lut));
+    return 0;
+}
+
+int fluid_streamlines(fluid_handle* h, const fluid_streamline_params* params, int max_lines, long long max_points,
+                      int* n_lines, long long* n_points, int* line_len, double* norm_speed, double* points)
+{
+    return fl_streamlines(h, params, max_lines, max_points, n_lines, n_points, line_len, norm_speed, points);
+}
+
 int fluid_add_density(fluid_handle* h, int n, const int* xyz, const float* amount)
 {
     if (int e = check_xyz(h, n, xyz, "fluid_add_density")) return e;

@@ -7,6 +7,7 @@
 #include "wavefront.cuh"
 #include "comm.cuh"
 #include "voxelize.cuh"
+#include "postproc.cuh"
 #include <cstring>
 #include <new>
 

@@ -225,6 +225,45 @@ class Simulation:
         self._ck(self._L.fluid_divergence_norm(self._h, out))
         return out[0], out[1]
 
+    # -- the offline viewers' arithmetic (gui.py:61-79, 265-300; GUI/utils.py:118-214) --------
+    def render_slice(self, field="dens", z=None, vmin=None, vmax=None, obstacle_alpha=0.2) -> np.ndarray:
+        """What gui.py's FluidViewer.update_image shows for plane `z` of `field`: an (h+2, w+2, 3) uint8
+        image, colour-mapped with the viewers' density_cmap and darkened over the obstacle.  vmin / vmax
+        default to the viewer's fixed ranges (gui.py:272-290)."""
+        rng = {"dens": (0.0, 0.01), "v_x": (-10.0, 10.0), "v_y": (-1.0, 1.0), "v_z": (-1.0, 1.0)}
+        name = field if isinstance(field, str) else FIELD_NAMES[int(field)]
+        lo, hi = rng.get(name, (0.0, 1.0))
+        vmin = lo if vmin is None else vmin
+        vmax = hi if vmax is None else vmax
+        z = (self.depth + 2) // 2 if z is None else int(z)
+        out = np.zeros((self.height + 2, self.width + 2, 3), dtype=np.uint8)
+        self._ck(self._L.fluid_render_slice(self._h, _fid(field), z, float(vmin), float(vmax), float(obstacle_alpha),
+                                            out.ctypes.data))
+        return out
+
+    def streamlines(self, density=30, proximity=2, integration_steps=100, step_size=0.2, velocity_change_threshold=0.1):
+        """GUI/utils.py generate_streamlines on the current velocity and obstacle fields (defaults =
+        GUI/config.py:19-24).  Returns (lines, norm_speed): a list of (n_i, 3) float64 arrays of padded
+        [x, y, z] positions in the reference's order, and per line the argument of its speed colour."""
+        from .viewer import StreamlineParams
+        sp = StreamlineParams(int(density), float(proximity), int(integration_steps), float(step_size),
+                              float(velocity_change_threshold))
+        half = sp.integration_steps // 2
+        max_lines = max(1, sp.density * (sp.density // 2) ** 2)
+        max_points = max_lines * (2 * half + 1)
+        nl, npnt = C.c_int(0), C.c_longlong(0)
+        # sizes first (no copy), then buffers that fit exactly
+        rc = self._L.fluid_streamlines(self._h, C.byref(sp), 0, 0, C.byref(nl), C.byref(npnt), None, None, None)
+        if rc != 0 and not (nl.value or npnt.value):
+            self._ck(rc)
+        if nl.value == 0:
+            return [], np.zeros(0)
+        assert nl.value <= max_lines and npnt.value <= max_points
+        lens = np.zeros(nl.value, np.int32); norm = np.zeros(nl.value); pts = np.zeros((npnt.value, 3))
+        self._ck(self._L.fluid_streamlines(self._h, C.byref(sp), nl.value, npnt.value, C.byref(nl), C.byref(npnt),
+                                           lens.ctypes.data, norm.ctypes.data, pts.ctypes.data))
+        return np.split(pts, np.cumsum(lens)[:-1]), norm
+
     def launch_count(self) -> int:
         return int(self._L.fluid_launch_count(self._h))
 

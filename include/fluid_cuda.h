@@ -139,6 +139,39 @@ int fluid_stats(fluid_handle*, double out[9]);
 /* sqrt(sum div^2) and max|div| of the stored divergence field over interior fluid cells */
 int fluid_divergence_norm(fluid_handle*, double out[2]);
 
+/* ---- the offline viewers' arithmetic on the resident fields; single-GPU handles only.
+ * The viewers' Qt windows and OpenGL draw calls are not reproduced: these return what they would draw. ---- */
+
+/* gui.py:61-79 + 265-300 (FluidViewer.update_image): plane z (0..d+1) of `field_id` colour-mapped with the
+ * viewers' density_cmap (Normalize(vmin, vmax, clip=True), 256 entries) to RGB888 and darkened by
+ * (1 - obstacle_alpha) where obs > 0.5 (the viewer uses 0.2).  rgb_host receives (h+2) rows x (w+2) columns x 3
+ * bytes, row y, column x, exactly the array the viewer hands to QImage.  Blocking. */
+int fluid_render_slice(fluid_handle*, int field_id, int z, double vmin, double vmax, double obstacle_alpha,
+                       unsigned char* rgb_host);
+
+/* the 256 x 3 float64 table behind that colour map (LinearSegmentedColormap.from_list over the seven named
+ * colours of gui.py:38-41 / GUI/config.py:14-17); host-only, needs no device */
+int fluid_density_cmap(double lut[768]);
+
+/* GUI/utils.py:118-214 generate_streamlines on the current v_x, v_y, v_z, obs (float64 arithmetic on the
+ * float32 fields, padded [x, y, z] coordinates as in GUI/main_window.py:227-230): seeds on the
+ * density x density/2 x density/2 lattice near the obstacle's bounding box, unit-speed integration of
+ * integration_steps/2 steps backward and forward (:83-115), the length / velocity-change / proximity
+ * filters (:173-198).  Accepted lines come back in the reference's order: line_len[i] points each, packed
+ * x, y, z in `points`; norm_speed[i] = min(max |v| on the line / (max(v_x, v_y, v_z) + 1e-6), 1), the
+ * argument of the viewers' colour map (:203-208).  n_lines / n_points always receive the totals; if they
+ * exceed max_lines / max_points the call fails with FLUID_E_ARG and copies nothing (worst case:
+ * density * (density/2)^2 lines of 2 * (integration_steps/2) + 1 points).  Blocking. */
+typedef struct fluid_streamline_params {
+    int density;                        /* STREAMLINE_DENSITY            GUI/config.py:20 (30) */
+    double proximity;                   /* STREAMLINE_PROXIMITY          :21 (2)               */
+    int integration_steps;              /* INTEGRATION_STEPS             :22 (100)             */
+    double step_size;                   /* INTEGRATION_STEP_SIZE         :23 (0.2)             */
+    double velocity_change_threshold;   /* VELOCITY_CHANGE_THRESHOLD     :24 (0.1)             */
+} fluid_streamline_params;
+int fluid_streamlines(fluid_handle*, const fluid_streamline_params* params, int max_lines, long long max_points,
+                      int* n_lines, long long* n_points, int* line_len, double* norm_speed, double* points);
+
 int fluid_sync(fluid_handle*);
 const char* fluid_last_error(fluid_handle*);
 

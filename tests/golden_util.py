@@ -9,9 +9,9 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 def golden_cases():
-    # solver goldens only; vox_*.npz belong to tests/test_voxelize.py
+    # solver goldens only; vox_*.npz belong to tests/test_voxelize.py, pp_*.npz to tests/test_postproc.py
     return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz"))
-                  if not os.path.basename(p).startswith("vox_"))
+                  if not os.path.basename(p).startswith(("vox_", "pp_")))
 
 
 def load_golden(name):
