@@ -4,6 +4,10 @@
 //   fluid_tunnel [--w 128 --h 64 --d 64 --iter 100 --acc 15 --speed 30] [--obstacle none|sphere|box|FILE.bin|FILE.stl]
 //                [--restart DIR[:FRAME]] [--stl-scale 0.8 --stl-rot rx,ry,rz --stl-translate tx,ty,tz --stl-sampling hashed|fixed|cells]
 //                [--solver rb|jacobi|lex] [--elide] [--out data] [--dump-every 1] [--quiet]
+//                [--view-ppm FILE [--view-field dens|v_x|v_y|v_z] [--view-z N]] [--view-streamlines FILE]
+// --view-*: after the run, what the reference's viewers would draw from the last frame (gui.py:265-300 z-slice as a
+// binary PPM; GUI/utils.py:118-214 streamlines as text: "line <n> <norm_speed>" followed by n "x y z" rows, origin
+// shifted by -1 as GUI/main_window.py:236 does), computed on the device.
 // FILE.bin = raw float32 padded mask (w+2)(h+2)(d+2) in the reference layout, e.g. dumped once from the
 // reference's STL loader (its output is not reproducible run to run).
 #include "simulation.h"
@@ -39,7 +43,8 @@ static std::vector<float> analytic_mask(const std::string& kind, int w, int h, i
 int main(int argc, char** argv)
 {
     int w = 128, h = 64, d = 64, iter = 100, acc = 15, speed = 30, dump_every = 1;   // simulation.cpp:431-436
-    std::string obstacle = "none", solver = "rb", out = "data", restart;
+    std::string obstacle = "none", solver = "rb", out = "data", restart, view_ppm, view_lines, view_field = "dens";
+    int view_z = -1;
     bool elide = false, quiet = false;
     float stl_scale = 0.8f, stl_rot[3] = { 0, 0, 0 }, stl_tr[3] = { 0, 0, 0 };      // loadSTLIntoObstacles defaults
     int stl_sampling = FLUID_VOX_HASHED;
@@ -54,6 +59,8 @@ int main(int argc, char** argv)
         else if (a == "--out") out = val(); else if (a == "--dump-every") dump_every = std::atoi(val());
         else if (a == "--elide") elide = true; else if (a == "--quiet") quiet = true;
         else if (a == "--restart") restart = val();
+        else if (a == "--view-ppm") view_ppm = val(); else if (a == "--view-streamlines") view_lines = val();
+        else if (a == "--view-field") view_field = val(); else if (a == "--view-z") view_z = std::atoi(val());
         else if (a == "--stl-scale") stl_scale = (float)std::atof(val());
         else if (a == "--stl-rot") triple(val(), stl_rot); else if (a == "--stl-translate") triple(val(), stl_tr);
         else if (a == "--stl-sampling") { std::string m = val(); stl_sampling = m == "fixed" ? FLUID_VOX_FIXED : m == "cells" ? FLUID_VOX_CELLS : FLUID_VOX_HASHED; }
@@ -85,6 +92,33 @@ int main(int argc, char** argv)
             if (!quiet) std::cout << "restarted from frame " << k << "\n";
         }
         sim.run();
+        if (!view_ppm.empty()) {                     // gui.py:265-300 with the viewer's fixed ranges (:272-290)
+            const int fid = view_field == "v_x" ? FLUID_VX : view_field == "v_y" ? FLUID_VY : view_field == "v_z" ? FLUID_VZ : FLUID_DENS;
+            const double lo = fid == FLUID_DENS ? 0.0 : fid == FLUID_VX ? -10.0 : -1.0, hi = fid == FLUID_DENS ? 0.01 : fid == FLUID_VX ? 10.0 : 1.0;
+            std::vector<unsigned char> rgb((size_t)(w + 2) * (h + 2) * 3);
+            if (fluid_render_slice(sim.handle(), fid, view_z < 0 ? (d + 2) / 2 : view_z, lo, hi, 0.2, rgb.data()) != 0)
+                throw std::runtime_error(std::string("render_slice: ") + fluid_last_error(sim.handle()));
+            std::ofstream f(view_ppm, std::ios::binary);
+            f << "P6\n" << w + 2 << " " << h + 2 << "\n255\n";
+            f.write((const char*)rgb.data(), (std::streamsize)rgb.size());
+        }
+        if (!view_lines.empty()) {                   // GUI/config.py:19-24 defaults
+            const fluid_streamline_params sp = { 30, 2.0, 100, 0.2, 0.1 };
+            const int max_lines = 30 * 15 * 15; const long long max_points = (long long)max_lines * 101;
+            std::vector<int> len(max_lines); std::vector<double> norm(max_lines), pts((size_t)max_points * 3);
+            int nl = 0; long long np = 0;
+            if (fluid_streamlines(sim.handle(), &sp, max_lines, max_points, &nl, &np, len.data(), norm.data(), pts.data()) != 0)
+                throw std::runtime_error(std::string("streamlines: ") + fluid_last_error(sim.handle()));
+            std::FILE* f = std::fopen(view_lines.c_str(), "w");
+            if (!f) throw std::runtime_error("cannot write " + view_lines);
+            size_t k = 0;
+            for (int i = 0; i < nl; ++i) {
+                std::fprintf(f, "line %d %.17g\n", len[i], norm[i]);
+                for (int j = 0; j < len[i]; ++j, ++k) std::fprintf(f, "%.17g %.17g %.17g\n", pts[3 * k] - 1, pts[3 * k + 1] - 1, pts[3 * k + 2] - 1);
+            }
+            std::fclose(f);
+            if (!quiet) std::cout << nl << " streamlines, " << np << " points -> " << view_lines << "\n";
+        }
         if (!quiet) {
             const double cells = (double)w * h * d;
             std::cout << fluid_version() << "\n" << sim.msPerStepLastRun() << " ms per step (incl. frame dumps), "

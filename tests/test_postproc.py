@@ -207,3 +207,42 @@ def test_gpu_slice_special_values(tmp_path):
         assert raw.startswith(b"P6\n23 11\n255\n") and len(raw) == 13 + 23 * 11 * 3
         with pytest.raises(Exception, match="bad argument"):
             sim.render_slice("dens", d + 2)
+
+
+@pytest.mark.gpu
+def test_driver_and_headless_viewer_outputs(tmp_path):
+    """fluid_tunnel --view-* (C++ host) and `python -m fluid_simulation_b200.viewer` on the frames it wrote:
+    both must give what the checker computes from the CPU solver's last frame."""
+    import oracle
+    from fluid_simulation_b200 import masks
+    w, h, d, acc, iters = 40, 24, 24, 6, 5
+    out = tmp_path / "data"; out.mkdir()
+    tunnel = os.path.join(ROOT, "fluid_simulation_b200", "host", "fluid_tunnel")
+    res = subprocess.run([tunnel, "--w", str(w), "--h", str(h), "--d", str(d), "--iter", str(iters), "--acc", str(acc),
+                          "--obstacle", "sphere", "--out", str(out), "--view-ppm", str(tmp_path / "a.ppm"), "--view-field", "v_x",
+                          "--view-z", "11", "--view-streamlines", str(tmp_path / "a.txt")], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    cpu = oracle.OracleSim(w, h, d, acc=acc, order=oracle.ORDER_RB)
+    cpu.set("obs", masks.sphere(w, h, d)); cpu.run_iterations(iters)
+    st = {k: cpu.get(k) for k in ("v_x", "v_y", "v_z", "obs", "dens")}
+    head = b"P6\n%d %d\n255\n" % (w + 2, h + 2)
+    assert (tmp_path / "a.ppm").read_bytes() == head + opp.render_slice(st["v_x"], st["obs"], 11, -10.0, 10.0).tobytes()
+    lines, norm = opp.streamlines(st["v_x"], st["v_y"], st["v_z"], st["obs"])
+    txt = (tmp_path / "a.txt").read_text().split("\n")
+    got_len = [int(l.split()[1]) for l in txt if l.startswith("line")]
+    got_norm = [float(l.split()[2]) for l in txt if l.startswith("line")]
+    got_pts = np.array([[float(v) for v in l.split()] for l in txt if l and not l.startswith("line")]).reshape(-1, 3)
+    assert got_len == [len(l) for l in lines] and np.array_equal(np.array(got_norm), norm)
+    if lines:
+        assert np.array_equal(got_pts, np.concatenate(lines) - 1)                     # %.17g round-trips float64
+    # the Python headless viewer on the same frame files
+    res = subprocess.run([sys.executable, "-m", "fluid_simulation_b200.viewer", str(out), "--field", "dens", "--z", "13",
+                          "--ppm", str(tmp_path / "b.ppm"), "--streamlines", str(tmp_path / "b.npz")],
+                         capture_output=True, text=True, cwd=ROOT)
+    assert res.returncode == 0, res.stderr
+    assert (tmp_path / "b.ppm").read_bytes() == head + opp.render_slice(st["dens"], st["obs"], 13, 0.0, 0.01).tobytes()
+    z = np.load(tmp_path / "b.npz")
+    assert list(z["line_len"]) == [len(l) for l in lines] and np.array_equal(z["norm_speed"], norm)
+    assert z["rgba"].shape == (len(lines), 4)
+    if lines:
+        assert np.array_equal(z["points"], np.concatenate(lines) - 1)
