@@ -126,37 +126,47 @@ __global__ void __launch_bounds__(256) k_divergence(Grid g, const float* __restr
 // one-sided / central pressure difference (simulation.cpp:328-336 and the y, z copies) in select
 // form: both open -> (p+ - p-)/(2h); only + -> (p+ - p)/h; only - -> (p - p-)/h; none -> 0.
 // One division per axis instead of three divergent ones (the kernel was issue bound on them).
-__device__ __forceinline__ float fl_axis_grad(bool po, bool mo, float pp, float pc, float pm, float h, float h2)
+// POW2: h is a power of two (every cubic 2^k grid: h = 1/cbrtf(W*H*D) = 2^-k), so x / h == x * (1/h) and
+// x / (2h) == x * (1/(2h)) bit for bit for EVERY float x (exact scaling; zeros keep their sign, denormals,
+// infinities and NaNs behave the same): s1 = 1/h, s2 = 1/(2h) and the quotient is one FMUL.  The IEEE
+// division it replaces is ~15 instructions on its fast path and a ~100-instruction subroutine whenever the
+// numerator is zero or denormal -- which the far field of the pressure solve is full of.  Otherwise
+// s1 = h, s2 = 2h and the division stays.
+template <bool POW2>
+__device__ __forceinline__ float fl_axis_grad(bool po, bool mo, float pp, float pc, float pm, float s1, float s2)
 {
     const float hi = po ? pp : pc, lo = mo ? pm : pc;
-    const float q = (hi - lo) / ((po && mo) ? h2 : h);
+    const float sc = (po && mo) ? s2 : s1;
+    const float q = POW2 ? (hi - lo) * sc : (hi - lo) / sc;
     return (po || mo) ? q : 0.0f;
 }
 
+// flag bit `m` of lane i in the packed flag word of a quad (one LOP3 with a predicate result)
+#define FL_QBIT(f4, i, m) (((f4) & ((unsigned)(m) << (8 * (i)))) != 0u)
+
 // ---- project part 3: v -= grad p on fluid cells, then setBounds(1..3) (:322-361) -------------
+template <bool POW2>
 __global__ void __launch_bounds__(256) k_gradient(Grid g, const float* __restrict__ p,
                                                   const unsigned char* __restrict__ flags,
                                                   float* __restrict__ vx, float* __restrict__ vy,
-                                                  float* __restrict__ vz, float h)
+                                                  float* __restrict__ vz, float s1, float s2)
 {
     QuadPos qp = fl_quad_pos(g, 1 + blockIdx.z);
     if (!qp.valid) return;
     const long long c = fl_idx(g, qp.x0, qp.y, qp.zl);
     const unsigned f4 = *reinterpret_cast<const unsigned*>(flags + c);
-    const unsigned fl[4] = { f4 & 0xffu, (f4 >> 8) & 0xffu, (f4 >> 16) & 0xffu, f4 >> 24 };
     Quad7 q; fl_load_quad7(g, p, c, q);
     const float4 ax = ld4(vx + c), ay = ld4(vy + c), az = ld4(vz + c);
     float rx[4] = { ax.x, ax.y, ax.z, ax.w }, ry[4] = { ay.x, ay.y, ay.z, ay.w },
           rz[4] = { az.x, az.y, az.z, az.w };
-    const float h2 = 2.0f * h;                                    // :330 (2.0f * h)
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const float pxp = (i == 3) ? q.xp : q.c[i + 1];
         const float pxm = (i == 0) ? q.xm : q.c[i - 1];
-        const float gx = fl_axis_grad(fl[i] & FL_OPEN_XP, fl[i] & FL_OPEN_XM, pxp, q.c[i], pxm, h, h2);
-        const float gy = fl_axis_grad(fl[i] & FL_OPEN_YP, fl[i] & FL_OPEN_YM, q.yp[i], q.c[i], q.ym[i], h, h2);
-        const float gz = fl_axis_grad(fl[i] & FL_OPEN_ZP, fl[i] & FL_OPEN_ZM, q.zp[i], q.c[i], q.zm[i], h, h2);
-        const bool solid = fl[i] & FL_SOLID;                      // :326 solids keep their value
+        const float gx = fl_axis_grad<POW2>(FL_QBIT(f4, i, FL_OPEN_XP), FL_QBIT(f4, i, FL_OPEN_XM), pxp, q.c[i], pxm, s1, s2);
+        const float gy = fl_axis_grad<POW2>(FL_QBIT(f4, i, FL_OPEN_YP), FL_QBIT(f4, i, FL_OPEN_YM), q.yp[i], q.c[i], q.ym[i], s1, s2);
+        const float gz = fl_axis_grad<POW2>(FL_QBIT(f4, i, FL_OPEN_ZP), FL_QBIT(f4, i, FL_OPEN_ZM), q.zp[i], q.c[i], q.zm[i], s1, s2);
+        const bool solid = FL_QBIT(f4, i, FL_SOLID);              // :326 solids keep their value
         rx[i] = solid ? rx[i] : rx[i] - gx;
         ry[i] = solid ? ry[i] : ry[i] - gy;
         rz[i] = solid ? rz[i] : rz[i] - gz;
@@ -244,4 +254,114 @@ __global__ void __launch_bounds__(256) k_advect(Grid g, int b, float* __restrict
                       *reinterpret_cast<const unsigned*>(flags + c), b, fl_edge_bits(g, qp.x0, qp.y, qp.zl));
     else
         fl_store_bounded(g, field, flags, b, qp.x0, qp.y, qp.zl, raw);
+}
+
+// ld.global.nc as a volatile asm: the compiler keeps volatile asm statements in program order, so a batch of
+// these loads is issued as written and cannot be sunk behind a later store (it does that with __ldg).
+__device__ __forceinline__ float fl_ldnc(const float* p)
+{
+    float v;
+    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+
+// ---- advect, lanes along x, NY rows per thread -------------------------------------------------------
+// The quad form above is bound by L1 and by issue (ncu: l1tex 89 %, issue 82 %): a warp's gather of
+// "corner k of lane cell i" strides 16 B from lane to lane, so each of the 32 scalar loads of a thread
+// touches four 128-byte lines, and a third of its instructions are 64-bit address arithmetic.  Here
+// consecutive lanes sit on consecutive x cells: the eight gathers are contiguous across the warp wherever the
+// back-trace is smooth (one or two lines per load), the own-cell loads and the store are plain coalesced
+// scalars, every index is a 32-bit element offset (one IMAD.WIDE per address; the host uses this kernel only
+// when the pitched volume has fewer than 2^31 cells), and a thread walks NY rows to amortise its set-up.
+// SLAB = false: one GPU, every plane lives in src.base[0].
+// Same statements, same operand order as k_advect: bit-identical results.
+template <bool SLAB, int NY>
+__global__ void __launch_bounds__(256) k_advect_rows(Grid g, int b, float* __restrict__ field,
+                                                     const float* __restrict__ prev_local, GatherSrc src,
+                                                     const float* __restrict__ vxf, const float* __restrict__ vyf,
+                                                     const float* __restrict__ vzf,
+                                                     const unsigned char* __restrict__ flags, float dt)
+{
+    const int x = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+    const int ya = 1 + (blockIdx.y * blockDim.y + threadIdx.y) * NY;
+    const int zl = 1 + blockIdx.z;
+    if (x > g.W || ya > g.H) return;
+    const unsigned pitch = (unsigned)g.pitch, plane = (unsigned)g.plane;
+    const int gz = g.zlo + zl - 1;
+    const float fW = (float)g.W, fH = (float)g.H, fD = (float)g.D;
+    const float kx = dt * fW, ky = dt * fH, kz = dt * fD;                    // dt * width etc. (:384-386, left to right)
+    const float hx = fW + 0.5f, hy = fH + 0.5f, hz = fD + 0.5f;
+    const float* __restrict__ ux = b == 1 ? prev_local : vxf;                // :380-382
+    const float* __restrict__ uy = b == 2 ? prev_local : vyf;
+    const float* __restrict__ uz = b == 3 ? prev_local : vzf;
+    const float* __restrict__ gsrc = src.base[0];
+    const int zoff = 1 - src.zlo[0];
+    const unsigned zm = fl_zero_mask(b);
+    const bool xz_edge = x == 1 || x == g.W || gz == 1 || gz == g.D;
+    const float fx = (float)x, fz = (float)gz;
+    const unsigned c0 = FL_XOFF + (unsigned)x + (unsigned)ya * pitch + (unsigned)zl * plane;
+    // Three phases without a branch between them, so that all NY flag / velocity loads and then all 8 * NY
+    // gathers of a thread are in flight together (the row-by-row form was a chain of 3 * NY memory round trips).
+    // Rows past H repeat row ya and are not stored; solid cells back-trace with zero velocity (their result is
+    // discarded, :375-378) so that whatever their stored velocity is, the gather address stays inside the volume.
+    unsigned cc[NY], fl[NY];
+    float vx[NY], vy[NY], vz[NY];
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {
+        cc[j] = (ya + j <= g.H) ? c0 + (unsigned)j * pitch : c0;
+        fl[j] = flags[cc[j]];
+        vx[j] = ux[cc[j]]; vy[j] = uy[cc[j]]; vz[j] = uz[cc[j]];
+    }
+    float sx[NY], sy[NY], sz[NY], q[NY][8];
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {
+        const bool solid = fl[j] & FL_SOLID;
+        const float fy = (float)((ya + j <= g.H) ? ya + j : ya);
+        float xb = fx - kx * (solid ? 0.0f : vx[j]);                         // :384-386
+        float yb = fy - ky * (solid ? 0.0f : vy[j]);
+        float zb = fz - kz * (solid ? 0.0f : vz[j]);
+        xb = fl_clamp(xb, 0.5f, hx);                                         // :388-390
+        yb = fl_clamp(yb, 0.5f, hy);
+        zb = fl_clamp(zb, 0.5f, hz);
+        const float fi = floorf(xb), fj = floorf(yb), fk = floorf(zb);       // :392-397
+        sx[j] = xb - fi; sy[j] = yb - fj; sz[j] = zb - fk;                   // :399-401
+        const int i0 = (int)fi, j0 = (int)fj, k0 = (int)fk;
+        if (SLAB) {
+            const float* __restrict__ q0 = fl_gather_plane(g, src, k0) + (i0 + j0 * (int)pitch);
+            const float* __restrict__ q1 = fl_gather_plane(g, src, k0 + 1) + (i0 + j0 * (int)pitch);
+            q[j][0] = fl_ldnc(q0); q[j][1] = fl_ldnc(q0 + 1); q[j][2] = fl_ldnc(q0 + pitch); q[j][3] = fl_ldnc(q0 + pitch + 1);
+            q[j][4] = fl_ldnc(q1); q[j][5] = fl_ldnc(q1 + 1); q[j][6] = fl_ldnc(q1 + pitch); q[j][7] = fl_ldnc(q1 + pitch + 1);
+        } else {
+            const unsigned o00 = FL_XOFF + (unsigned)i0 + (unsigned)j0 * pitch + (unsigned)(k0 + zoff) * plane;
+            const unsigned o10 = o00 + pitch, o01 = o00 + plane, o11 = o01 + pitch;
+            q[j][0] = fl_ldnc(gsrc + o00); q[j][1] = fl_ldnc(gsrc + o00 + 1); q[j][2] = fl_ldnc(gsrc + o10); q[j][3] = fl_ldnc(gsrc + o10 + 1);
+            q[j][4] = fl_ldnc(gsrc + o01); q[j][5] = fl_ldnc(gsrc + o01 + 1); q[j][6] = fl_ldnc(gsrc + o11); q[j][7] = fl_ldnc(gsrc + o11 + 1);
+        }
+    }
+    asm volatile("" ::: "memory");     // every gather is issued before the first store (the compiler would sink rows 1.. behind it)
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {
+        const int y = ya + j;
+        if (y > g.H) break;
+        const float tx = 1.0f - sx[j], ty = 1.0f - sy[j], tz = 1.0f - sz[j];
+        const float c00 = q[j][0] * tx + q[j][1] * sx[j];                    // :412-415  (c000, c100)
+        const float c01 = q[j][4] * tx + q[j][5] * sx[j];                    //           (c001, c101)
+        const float c10 = q[j][2] * tx + q[j][3] * sx[j];                    //           (c010, c110)
+        const float c11 = q[j][6] * tx + q[j][7] * sx[j];                    //           (c011, c111)
+        const float e0 = c00 * ty + c10 * sy[j];                             // :417-418
+        const float e1 = c01 * ty + c11 * sy[j];
+        const float raw = (fl[j] & FL_SOLID) ? 0.0f : e0 * tz + e1 * sz[j];  // :420, :375-378
+        // setBounds(b, field) (:183-246): ghosts take the pre-zero value, then solids / no-slip cells are zeroed
+        const unsigned c = cc[j];
+        field[c] = (fl[j] & zm) ? 0.0f : raw;
+        if (xz_edge || y == 1 || y == g.H) {
+            if (x == 1)   field[c - 1] = (b == 1) ? -raw : raw;              // :189
+            if (x == g.W) field[c + 1] = raw;                                // :191
+            const float gy = (b == 2) ? -raw : raw, gzv = (b == 3) ? -raw : raw;
+            if (y == 1)   field[c - pitch] = gy;                             // :198-201
+            if (y == g.H) field[c + pitch] = gy;
+            if (gz == 1)   field[c - plane] = gzv;                           // :208-214
+            if (gz == g.D) field[c + plane] = gzv;
+        }
+    }
 }

@@ -7,6 +7,8 @@
 #include "kernels_stencil.cuh"
 #include "kernels_reduce.cuh"
 #include <math.h>
+#include <string.h>
+#include <stdlib.h>
 
 int fl_halo_exchange(fluid_handle* h, int n, float* const* fields);      // comm.cuh (slab mode)
 int fl_lex_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
@@ -168,9 +170,18 @@ static inline int fl_gradient(fluid_handle* h)
 {
     if (int e = fl_rebuild_flags(h)) return e;
     QuadLaunch q = fl_quad_launch(h->g, h->g.Dl);
-    k_gradient<<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags,
-                                                  h->field[FLUID_VX], h->field[FLUID_VY],
-                                                  h->field[FLUID_VZ], fl_project_h(h));
+    // h a power of two (cubic 2^k grids): x / h and x / (2h) are exact scalings, done as multiplications
+    const float hh = fl_project_h(h), h2 = 2.0f * hh;                       // :330 (2.0f * h)
+    unsigned hb; memcpy(&hb, &hh, sizeof hb);
+    const unsigned he = (hb >> 23) & 0xffu;
+    static const bool no_pow2 = getenv("FLUID_GRAD_DIV") != nullptr;        // A/B: always divide
+    const bool pow2 = !no_pow2 && (hb & 0x007fffffu) == 0u && he >= 2u && he <= 252u;   // 1/h, 1/(2h) normal and exact
+    if (pow2)
+        k_gradient<true><<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags, h->field[FLUID_VX],
+                                                            h->field[FLUID_VY], h->field[FLUID_VZ], 1.0f / hh, 1.0f / h2);
+    else
+        k_gradient<false><<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags, h->field[FLUID_VX],
+                                                             h->field[FLUID_VY], h->field[FLUID_VZ], hh, h2);
     FL_CHECK_LAUNCH(h);
     if (h->nranks > 1) {
         float* f[3] = { h->field[FLUID_VX], h->field[FLUID_VY], h->field[FLUID_VZ] };
@@ -195,10 +206,25 @@ static inline int fl_advect(fluid_handle* h, int b, int fid, int pid)     // sim
     GatherSrc src;
     if (int e = fl_gather_sources(h, pid, &src)) return e;
     if (int e = fl_barrier(h)) return e;          // every rank's slab of the gather source is complete
-    QuadLaunch q = fl_quad_launch(h->g, h->g.Dl);
-    k_advect<<<q.grid, q.block, 0, h->stream>>>(h->g, b, h->field[fid], h->field[pid], src,
-                                                h->field[FLUID_VX], h->field[FLUID_VY],
-                                                h->field[FLUID_VZ], h->cflags, h->dt);
+    static const bool quad = getenv("FLUID_ADVECT_QUAD") != nullptr;        // A/B: the one-thread-per-quad form
+    if (quad || h->g.cells >= (1ll << 31)) {
+        QuadLaunch q = fl_quad_launch(h->g, h->g.Dl);
+        k_advect<<<q.grid, q.block, 0, h->stream>>>(h->g, b, h->field[fid], h->field[pid], src,
+                                                    h->field[FLUID_VX], h->field[FLUID_VY],
+                                                    h->field[FLUID_VZ], h->cflags, h->dt);
+    } else {
+        static const int ny_env = getenv("FLUID_ADVECT_NY") ? atoi(getenv("FLUID_ADVECT_NY")) : 0;
+        const int NY = (ny_env == 1 || ny_env == 2 || ny_env == 4) ? ny_env : 2;            // rows per thread (2: measured best, 86 vs 92 us at 256^3)
+        int bx = 32;
+        while (bx < h->g.W && bx < 128) bx <<= 1;
+        const dim3 block(bx, 256 / bx, 1);
+        const dim3 grid((h->g.W + bx - 1) / bx, (h->g.H + block.y * NY - 1) / (block.y * NY), h->g.Dl);
+#define FL_ADV_LAUNCH(SLAB, N) k_advect_rows<SLAB, N><<<grid, block, 0, h->stream>>>(h->g, b, h->field[fid], h->field[pid], src, \
+                                   h->field[FLUID_VX], h->field[FLUID_VY], h->field[FLUID_VZ], h->cflags, h->dt)
+        if (src.n > 1) { if (NY == 1) FL_ADV_LAUNCH(true, 1); else if (NY == 2) FL_ADV_LAUNCH(true, 2); else FL_ADV_LAUNCH(true, 4); }
+        else           { if (NY == 1) FL_ADV_LAUNCH(false, 1); else if (NY == 2) FL_ADV_LAUNCH(false, 2); else FL_ADV_LAUNCH(false, 4); }
+#undef FL_ADV_LAUNCH
+    }
     FL_CHECK_LAUNCH(h);
     if (h->nranks > 1) {
         float* f[1] = { h->field[fid] };
