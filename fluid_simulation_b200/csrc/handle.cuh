@@ -39,6 +39,9 @@ struct fluid_handle {
     struct ProfRec { cudaEvent_t a, b; long long field_sweeps; };
     std::vector<ProfRec> prof;
     std::vector<cudaEvent_t> ev_pool;
+    // set by fl_step_only when it swapped v <-> v_prev instead of copying: the next tiled solve takes its initial
+    // guess from the right-hand-side buffer (which holds the very same values) and clears the flag
+    bool x_from_rhs = false;
     int sm_count = 148;
     size_t l2_persist_max = 0, l2_window_max = 0;   // persisting-L2 carve-out and access-window limits
 };

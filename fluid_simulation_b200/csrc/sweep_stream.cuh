@@ -811,7 +811,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
 
 template <int TXW, int NP, int CPS>
 inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
-                  bool jacobi)
+                  bool jacobi, bool x_from_rhs)
 {
     using GE = SwGeom<TXW, NP, CPS>;
     const Grid& g = h->g;
@@ -853,7 +853,12 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     }
     dim3 ge((2 * (g.W + 2) + 2 * g.H + 127) / 128, g.Dl + 2);
     for (int i = 0; i < nb; ++i) {                                        // edge/corner ghosts follow
-        k_copy_edges<<<ge, 128, 0, h->stream>>>(g, cur[i], alt[i]);
+        if (x_from_rhs) {                                                 // field[fid] is a stale buffer: both partners take them from the guess
+            k_copy_edges<<<ge, 128, 0, h->stream>>>(g, h->field[pid[i]], cur[i]);
+            FL_CHECK_LAUNCH(h);
+            k_copy_edges<<<ge, 128, 0, h->stream>>>(g, h->field[pid[i]], alt[i]);
+        } else
+            k_copy_edges<<<ge, 128, 0, h->stream>>>(g, cur[i], alt[i]);
         FL_CHECK_LAUNCH(h);
     }
     // Single-field solves re-read the same right-hand side acc times: optionally pin it in the
@@ -871,9 +876,12 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         FL_CUDA(h, cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av));
     }
     for (int k = 0; k < h->acc; ++k) {                                    // simulation.cpp:258
+        // x_from_rhs: the first sweep reads its guess from the right-hand-side buffer (same values: the caller
+        // swapped the two fields instead of copying, simulation.cpp:108-110) and writes field[fid]
+        const bool first_from_rhs = x_from_rhs && k == 0;
         for (int i = 0; i < nb; ++i) {
-            if (int e = sw_get_map(h, cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
-            A.dst[i] = alt[i];
+            if (int e = sw_get_map(h, first_from_rhs ? h->field[pid[i]] : cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
+            A.dst[i] = first_from_rhs ? cur[i] : alt[i];
         }
         A.flip = (s->zigzag && (k & 1)) ? 1 : 0;         // odd sweeps stream the other way (L2 reuse)
         const sweep_kernel kern = kerns[mixed ? 2 : A.flip];
@@ -901,7 +909,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         } else
             kern<<<plan.nctas, GE::THREADS, GE::SMEM, h->stream>>>(A);
         FL_CHECK_LAUNCH(h);
-        for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
+        if (!first_from_rhs) for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
         if (fused) {
             // the next sweep's edge CTAs wait for the neighbours' halos themselves (sw_await_face);
             // whatever follows the solve waits once, below
@@ -928,6 +936,28 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     return 0;
 }
 
+// does the streaming kernel take this handle's solves?  (shapes it declines go to the simple kernels)
+inline bool fl_tiled_eligible(fluid_handle* h)
+{
+    const Grid& g = h->g;
+    const unsigned solver = h->flags & FLUID_SOLVER_MASK;
+    if (h->flags & FLUID_NO_TILED) return false;
+    if (solver != FLUID_SOLVER_RB && solver != FLUID_SOLVER_JACOBI) return false;
+    if ((g.W & 3) || g.W > 1024) return false;            // quads must not straddle the x = W+1 ghost
+    if (!(h->flags & FLUID_TILED_ALWAYS) && (g.W < 64 || g.H < 8 || g.Dl < 4)) return false;
+    return true;
+}
+
+// step() may swap v <-> v_prev instead of copying (simulation.cpp:108-110) when the solve that follows is an
+// out-of-place streaming solve on one GPU: its first sweep then reads the guess from the right-hand side
+inline bool fl_swap_instead_of_copy(fluid_handle* h)
+{
+    static const bool off = getenv("FLUID_NO_SWAP") != nullptr;
+    if (off || h->nranks != 1 || h->acc <= 0 || !fl_tiled_eligible(h)) return false;
+    StreamState* s = sw_state(h);
+    return s->encode != nullptr && !s->unbatch;
+}
+
 // linearSolver through the streaming kernel; *handled = false leaves the solve to the simple kernels
 inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
                           float a, float c, bool* handled)
@@ -935,9 +965,9 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
     *handled = false;
     const Grid& g = h->g;
     const unsigned solver = h->flags & FLUID_SOLVER_MASK;
-    if (solver != FLUID_SOLVER_RB && solver != FLUID_SOLVER_JACOBI) return 0;
-    if ((g.W & 3) || g.W > 1024) return 0;                // quads must not straddle the x = W+1 ghost
-    if (!(h->flags & FLUID_TILED_ALWAYS) && (g.W < 64 || g.H < 8 || g.Dl < 4)) return 0;
+    const bool x_from_rhs = h->x_from_rhs;
+    h->x_from_rhs = false;
+    if (!fl_tiled_eligible(h)) return x_from_rhs ? fl_fail(h, FLUID_E_STATE, "internal: swapped fields reached a non-streaming solve") : 0;
     StreamState* s = sw_state(h);
     if (!s->encode) return fl_fail(h, FLUID_E_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
     const bool jac = solver == FLUID_SOLVER_JACOBI;
@@ -947,14 +977,14 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
     for (int gi = 0; gi < ngroups; ++gi) {
         const int* bb = b + gi * per; const int* ff = fid + gi * per; const int* pp = pid + gi * per;
         int e;
-        if (g.W <= 128)      e = sw_run<1, 16, 1>(h, per, bb, ff, pp, a, c, jac);
+        if (g.W <= 128)      e = sw_run<1, 16, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
         else if (g.W <= 256) {
-            if (s->cfg == 1)      e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac);
-            else if (s->cfg == 2) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac);
-            else if (s->cfg == 3) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac);
-            else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac);
-        } else if (g.W <= 512) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac);
-        else                   e = sw_run<8, 2, 1>(h, per, bb, ff, pp, a, c, jac);   // two owned rows: x re-read twice
+            if (s->cfg == 1)      e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
+            else if (s->cfg == 2) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
+            else if (s->cfg == 3) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
+            else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
+        } else if (g.W <= 512) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
+        else                   e = sw_run<8, 2, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);   // two owned rows: x re-read twice
         if (e) return e;
     }
     *handled = true;

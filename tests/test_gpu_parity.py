@@ -68,6 +68,41 @@ def test_divergence_and_gradient(w, h, d):
     check(gpu, cpu, "gradient")
 
 
+@pytest.mark.parametrize("w,h,d", [(16, 16, 16), (64, 32, 16), (32, 8, 2), (16, 16, 8)])
+def test_gradient_extreme_pressures(w, h, d):
+    """Where h = 1/cbrtf(W*H*D) is a power of two (the first three shapes) k_gradient multiplies by 1/h
+    instead of dividing by h; the claim is that this is exact for EVERY float, so the pressure field holds
+    zeros of both signs, denormals, the smallest / largest normals and values whose differences overflow.
+    (16, 16, 8) has a non-power-of-two h and takes the dividing kernel on the same data.)"""
+    gpu, cpu = make_pair(w, h, d, 4, 0, ORDER_RB)
+    rng = np.random.default_rng(w * 131 + d)
+    shape = cpu.shape
+    mant = rng.integers(0, 1 << 23, shape, dtype=np.uint32)
+    sign = rng.integers(0, 2, shape, dtype=np.uint32) << 31
+    kind = rng.integers(0, 8, shape)
+    expo = np.select([kind == 0, kind == 1, kind == 2, kind == 3, kind == 4],
+                     [0, 1, 254, rng.integers(1, 30, shape), rng.integers(225, 255, shape)],
+                     rng.integers(100, 150, shape)).astype(np.uint32)
+    bits = sign | (expo << 23) | np.where(kind == 5, 0, mant).astype(np.uint32)     # kind 0: denormals / zeros, 5: powers of two
+    bits[kind == 6] = np.where(rng.integers(0, 2, int((kind == 6).sum())) == 0, 0x00000000, 0x80000000)   # +0 / -0
+    p = bits.view(np.float32)
+    assert np.isfinite(p).all() and (np.abs(p[p != 0]) < np.finfo(np.float32).tiny).any()
+    gpu.set("pressure", p); cpu.set("pressure", p)
+    for n in ("v_x", "v_y", "v_z"):            # zero velocity in half of the tunnel: there the result is -grad p itself
+        v = cpu.get(n); v[: shape[0] // 2] = 0.0
+        gpu.set(n, v); cpu.set(n, v)
+    gpu.gradient(); cpu.gradient()
+    got, want = gpu.state(), cpu.state()
+    tiny = np.finfo(np.float32).tiny
+    assert ((np.abs(want["v_x"]) < tiny) & (want["v_x"] != 0)).any()      # denormal quotients were exercised
+    for n in ("v_x", "v_y", "v_z"):
+        a, b = got[n], want[n]
+        nan = np.isnan(b)                      # inf - inf: NaN on both sides, payloads are not compared
+        assert np.array_equal(np.isnan(a), nan), n
+        assert np.array_equal(a.view(np.uint32)[~nan], b.view(np.uint32)[~nan]), n
+    assert np.isinf(want["v_x"]).any()         # overflowing differences were exercised
+
+
 @pytest.mark.parametrize("name,flag,order", SOLVERS)
 @pytest.mark.parametrize("w,h,d", SIZES)
 @pytest.mark.parametrize("b", [0, 2])
