@@ -152,7 +152,7 @@ void fluid_destroy(fluid_handle* h)
     fl_tiled_release(h);
     fl_comm_release(h);
     for (int i = 0; i < FLUID_NFIELDS; ++i) if (h->field[i]) cudaFree(h->field[i] - h->g.plane);
-    for (int i = 0; i < 3; ++i) if (h->scratch[i]) cudaFree(h->scratch[i] - h->g.plane);
+    for (int i = 0; i < 4; ++i) if (h->scratch[i]) cudaFree(h->scratch[i] - h->g.plane);
     for (int i = 0; i < 5; ++i) cudaFree(h->frame_staging[i]);
     if (h->cflags) cudaFree(h->cflags - h->g.plane);
     cudaFree(h->staging); cudaFree(h->d_partial); cudaFree(h->d_out);

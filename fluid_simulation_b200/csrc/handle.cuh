@@ -16,7 +16,7 @@ struct fluid_handle {
     cudaEvent_t ev_frame_packed = nullptr, ev_frame_done = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     float* field[FLUID_NFIELDS] = {};
-    float* scratch[3] = {};          // Jacobi ping-pong partners (up to 3 batched fields)
+    float* scratch[4] = {};          // ping-pong partners of the batched solves ([3]: allocated on first use, one GPU only)
     // Allocation starts (plane -1) in FLUID_IPC_* id order.  field[] / scratch[] are permuted by the
     // solver's pointer swaps, identically on every rank; a buffer's id is found by its address.
     float* alloc_base[FLUID_NFIELDS + 3] = {};
@@ -41,7 +41,7 @@ struct fluid_handle {
     std::vector<cudaEvent_t> ev_pool;
     // set by fl_step_only when it swapped v <-> v_prev instead of copying: the next tiled solve takes its initial
     // guess from the right-hand-side buffer (which holds the very same values) and clears the flag
-    bool x_from_rhs = false;
+    unsigned x_from_rhs = 0;         // bit i: batched field i
     int sm_count = 148;
     size_t l2_persist_max = 0, l2_window_max = 0;   // persisting-L2 carve-out and access-window limits
 };

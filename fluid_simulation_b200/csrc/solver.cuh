@@ -262,28 +262,36 @@ static inline int fl_copy_field(fluid_handle* h, int dst, int src)
 static inline int fl_step_only(fluid_handle* h)
 {
     if (int e = fl_inflow_velocity(h)) return e;                          // :103-105
-    if (fl_swap_instead_of_copy(h)) {
+    // The density diffusion of :135 reads only dens and buffer, which nothing between here and :135 touches, uses
+    // the same a and c as the velocity diffusions (:282-283) and its result is not read before :136.  On the
+    // streaming single-GPU path it therefore rides along as a fourth field of the batched velocity solve: same
+    // arithmetic, same results, 80 launches fewer and longer z-ranges per CTA (4 extra planes per range of ~130
+    // instead of per ~33).
+    static const bool no_batch4 = getenv("FLUID_NO_BATCH4") != nullptr;
+    const bool swap = fl_swap_instead_of_copy(h);
+    const bool batch4 = swap && !no_batch4 && !(h->flags & FLUID_ELIDE_DEAD);
+    if (swap) {
         // :108-110 v_prev = v without moving bytes: the buffers trade places (v_prev now holds v, v a stale buffer
         // that the out-of-place solve below overwrites completely) and the solve's first sweep reads its initial
         // guess -- which the copy would have made equal to v_prev -- from v_prev.  3 x 70 MB less traffic at 256^3.
         for (int k = 0; k < 3; ++k) { float* t = h->field[FLUID_VX + k]; h->field[FLUID_VX + k] = h->field[FLUID_VX_PREV + k]; h->field[FLUID_VX_PREV + k] = t; }
-        h->x_from_rhs = true;
+        h->x_from_rhs = 0x7u;
     } else {
         if (int e = fl_copy_field(h, FLUID_VX_PREV, FLUID_VX)) return e;  // :108-110
         if (int e = fl_copy_field(h, FLUID_VY_PREV, FLUID_VY)) return e;
         if (int e = fl_copy_field(h, FLUID_VZ_PREV, FLUID_VZ)) return e;
     }
     {   // :115-117 the three velocity diffusions share a and c -> one batched launch per sweep
-        const int b[3] = { 1, 2, 3 }, f[3] = { FLUID_VX, FLUID_VY, FLUID_VZ },
-                  p[3] = { FLUID_VX_PREV, FLUID_VY_PREV, FLUID_VZ_PREV };
-        if (int e = fl_diffuse(h, 3, b, f, p)) return e;
+        const int b[4] = { 1, 2, 3, 0 }, f[4] = { FLUID_VX, FLUID_VY, FLUID_VZ, FLUID_DENS },
+                  p[4] = { FLUID_VX_PREV, FLUID_VY_PREV, FLUID_VZ_PREV, FLUID_BUFFER };
+        if (int e = fl_diffuse(h, batch4 ? 4 : 3, b, f, p)) return e;
     }
     if (int e = fl_project(h)) return e;                                  // :120
     if (int e = fl_advect(h, 1, FLUID_VX, FLUID_VX_PREV)) return e;       // :125-127, in this order
     if (int e = fl_advect(h, 2, FLUID_VY, FLUID_VY_PREV)) return e;
     if (int e = fl_advect(h, 3, FLUID_VZ, FLUID_VZ_PREV)) return e;
     if (int e = fl_project(h)) return e;                                  // :130
-    if (!(h->flags & FLUID_ELIDE_DEAD)) {                                 // :135 (dead work, F2)
+    if (!(h->flags & FLUID_ELIDE_DEAD) && !batch4) {                      // :135 (dead work, F2)
         const int b = 0, f = FLUID_DENS, p = FLUID_BUFFER;
         if (int e = fl_diffuse(h, 1, &b, &f, &p)) return e;
     }

@@ -41,10 +41,10 @@
 struct SwSeg { int col, za, zb, mode; };
 
 struct alignas(64) StreamArgs {
-    CUtensorMap map[3];                  // source field of each batched solve (box SW_BOXW x BR x 1)
-    CUtensorMap rmap[3];                 // its right-hand side (box SW_RBOXW x BR-2 x 1)
-    float* dst[3];
-    int b[3];
+    CUtensorMap map[4];                  // source field of each batched solve (box SW_BOXW x BR x 1)
+    CUtensorMap rmap[4];                 // its right-hand side (box SW_RBOXW x BR-2 x 1)
+    float* dst[4];
+    int b[4];
     const unsigned char* flags;
     const SwSeg* segs;                   // CTA k works through segs[seg_first[k] .. seg_first[k+1])
     const int* seg_first;
@@ -811,7 +811,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
 
 template <int TXW, int NP, int CPS>
 inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
-                  bool jacobi, bool x_from_rhs)
+                  bool jacobi, unsigned x_from_rhs)
 {
     using GE = SwGeom<TXW, NP, CPS>;
     const Grid& g = h->g;
@@ -845,7 +845,14 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     A.segs = plan.segs; A.seg_first = plan.seg_first;
     A.dbg = s->dbg;
 
-    float* cur[3]; float* alt[3];
+    float* cur[4]; float* alt[4];
+    if (nb > 4 || (nb == 4 && h->nranks > 1)) return fl_fail(h, FLUID_E_ARG, "streaming solve: %d batched fields", nb);
+    if (nb == 4 && !h->scratch[3]) {                                      // fourth ping-pong partner, first use
+        const size_t fb = (size_t)g.cells * sizeof(float);
+        FL_CUDA(h, cudaMalloc(&h->scratch[3], fb));
+        FL_CUDA(h, cudaMemsetAsync(h->scratch[3], 0, fb, h->stream));
+        h->scratch[3] += g.plane;
+    }
     for (int i = 0; i < nb; ++i) {
         cur[i] = h->field[fid[i]]; alt[i] = h->scratch[i];
         A.b[i] = b[i];
@@ -853,7 +860,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     }
     dim3 ge((2 * (g.W + 2) + 2 * g.H + 127) / 128, g.Dl + 2);
     for (int i = 0; i < nb; ++i) {                                        // edge/corner ghosts follow
-        if (x_from_rhs) {                                                 // field[fid] is a stale buffer: both partners take them from the guess
+        if ((x_from_rhs >> i) & 1u) {                                     // field[fid] is a stale buffer: both partners take them from the guess
             k_copy_edges<<<ge, 128, 0, h->stream>>>(g, h->field[pid[i]], cur[i]);
             FL_CHECK_LAUNCH(h);
             k_copy_edges<<<ge, 128, 0, h->stream>>>(g, h->field[pid[i]], alt[i]);
@@ -878,10 +885,11 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     for (int k = 0; k < h->acc; ++k) {                                    // simulation.cpp:258
         // x_from_rhs: the first sweep reads its guess from the right-hand-side buffer (same values: the caller
         // swapped the two fields instead of copying, simulation.cpp:108-110) and writes field[fid]
-        const bool first_from_rhs = x_from_rhs && k == 0;
+        const unsigned from_rhs = k == 0 ? x_from_rhs : 0u;                // per batched field
         for (int i = 0; i < nb; ++i) {
-            if (int e = sw_get_map(h, first_from_rhs ? h->field[pid[i]] : cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
-            A.dst[i] = first_from_rhs ? cur[i] : alt[i];
+            const bool fr = (from_rhs >> i) & 1u;
+            if (int e = sw_get_map(h, fr ? h->field[pid[i]] : cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
+            A.dst[i] = fr ? cur[i] : alt[i];
         }
         A.flip = (s->zigzag && (k & 1)) ? 1 : 0;         // odd sweeps stream the other way (L2 reuse)
         const sweep_kernel kern = kerns[mixed ? 2 : A.flip];
@@ -909,7 +917,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         } else
             kern<<<plan.nctas, GE::THREADS, GE::SMEM, h->stream>>>(A);
         FL_CHECK_LAUNCH(h);
-        if (!first_from_rhs) for (int i = 0; i < nb; ++i) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
+        for (int i = 0; i < nb; ++i) if (!((from_rhs >> i) & 1u)) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
         if (fused) {
             // the next sweep's edge CTAs wait for the neighbours' halos themselves (sw_await_face);
             // whatever follows the solve waits once, below
@@ -965,8 +973,8 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
     *handled = false;
     const Grid& g = h->g;
     const unsigned solver = h->flags & FLUID_SOLVER_MASK;
-    const bool x_from_rhs = h->x_from_rhs;
-    h->x_from_rhs = false;
+    const unsigned x_from_rhs = h->x_from_rhs;
+    h->x_from_rhs = 0;
     if (!fl_tiled_eligible(h)) return x_from_rhs ? fl_fail(h, FLUID_E_STATE, "internal: swapped fields reached a non-streaming solve") : 0;
     StreamState* s = sw_state(h);
     if (!s->encode) return fl_fail(h, FLUID_E_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
