@@ -72,3 +72,28 @@ def test_product_never_touches_the_oracle():
                 assert "oracle" not in txt.replace("the CPU oracle", ""), os.path.join(dirpath, f)
     out = subprocess.run(["ldd", _lib.LIB_PATH], capture_output=True, text=True).stdout
     assert "oracle" not in out and "fluid_ref" not in out
+
+
+def test_streamline_params_layout_matches_ctypes(tmp_path):
+    """struct fluid_streamline_params crosses the ABI by pointer: the C layout (include/fluid_cuda.h) and the
+    ctypes mirror (fluid_simulation_b200/viewer.py) must agree on size and every offset."""
+    from fluid_simulation_b200.viewer import StreamlineParams
+    src = tmp_path / "layout.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "fluid_cuda.h"\nint main(void){'
+                   'printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(fluid_streamline_params), offsetof(fluid_streamline_params, density),'
+                   'offsetof(fluid_streamline_params, proximity), offsetof(fluid_streamline_params, integration_steps),'
+                   'offsetof(fluid_streamline_params, step_size), offsetof(fluid_streamline_params, velocity_change_threshold));return 0;}')
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    want = [C.sizeof(StreamlineParams)] + [getattr(StreamlineParams, n).offset for n in
+                                           ("density", "proximity", "integration_steps", "step_size", "velocity_change_threshold")]
+    assert got == want
+
+
+def test_header_compiles_as_plain_c(tmp_path):
+    """The boundary is a C ABI: the header must be usable from a C translation unit (no C++ in the signatures)."""
+    src = tmp_path / "h.c"
+    src.write_text('#include "fluid_cuda.h"\nint main(void){ return FLUID_NFIELDS == 11 ? 0 : 1; }\n')
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), "-c", str(src),
+                    "-o", str(tmp_path / "h.o")], check=True)
