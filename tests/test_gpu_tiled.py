@@ -62,6 +62,21 @@ def test_tiled_full_steps(name, flag, order):
 
 
 @pytest.mark.parametrize("name,flag,order", SOLVERS)
+@pytest.mark.parametrize("w,h,d", [(320, 24, 16), (512, 20, 12), (64, 40, 20)])
+def test_tiled_full_steps_other_column_counts(name, flag, order, w, h, d):
+    """Whole run() iterations through the four-warp-column (256 < W <= 512) and one-warp-column (W <= 128)
+    kernels: the 4-field diffusion launch, the v <-> v_prev swap and the dependent launches on those shapes."""
+    from fluid_simulation_b200 import Simulation, masks
+    acc = 5
+    gpu = Simulation(w, h, d, 1, acc=acc, flags=flag)
+    cpu = OracleSim(w, h, d, acc=acc, order=order)
+    obs = masks.box(w, h, d)
+    gpu.set("obs", obs); cpu.set("obs", obs)
+    gpu.run_iterations(2); cpu.run_iterations(2)
+    assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, f"tiled 2 iterations {w}x{h}x{d} [{name}]")
+
+
+@pytest.mark.parametrize("name,flag,order", SOLVERS)
 def test_tiled_equals_simple_kernels_256(name, flag, order):
     """A/B at a BASELINE-sized plane (256x256x48, airfoil): tiled vs global-memory kernels."""
     from fluid_simulation_b200 import Simulation, masks
