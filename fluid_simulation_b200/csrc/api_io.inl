@@ -143,9 +143,9 @@ int fluid_set_velocity(fluid_handle* h, int n, const int* xyz, const float* v)
     return 0;
 }
 
-// frame write of step(), simulation.cpp:140-148: dens, obs, v_x, v_y, v_z.  The fields are
-// repacked to the reference layout on the compute stream (cheap, HBM to HBM), then the D2H copies
-// run on the dump stream so the next time step overlaps the PCIe transfer.
+// frame write of step(), simulation.cpp:140-148: dens, obs, v_x, v_y, v_z.  One kernel on the compute
+// stream takes the snapshot (all requested fields repacked to the reference layout, HBM to HBM), then one
+// D2H copy per field runs on the dump stream so the next time step overlaps the PCIe transfer.
 int fluid_dump_frame_async(fluid_handle* h, float* const dst[5])
 {
     if (!h || !dst) return FLUID_E_ARG;
@@ -157,9 +157,14 @@ int fluid_dump_frame_async(fluid_handle* h, float* const dst[5])
         if (dst[i] && !h->frame_staging[i]) FL_CUDA(h, cudaMalloc(&h->frame_staging[i], nfl * sizeof(float)));
     // the previous dump must have left the staging buffers before they are overwritten
     if (h->frame_in_flight) FL_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_frame_done, 0));
+    PackBatch pb; int nf = 0;
     for (int i = 0; i < 5; ++i) {
         if (!dst[i]) continue;
-        k_pack<<<fl_grid_1d((long long)nfl), 256, 0, h->stream>>>(h->g, zf, np, h->field[ids[i]], h->frame_staging[i]);
+        pb.src[nf] = h->field[ids[i]]; pb.dst[nf] = h->frame_staging[i]; ++nf;
+    }
+    if (nf > 0) {                                         // one snapshot launch for the whole frame
+        const dim3 blk(64, 4), grd((unsigned)((h->g.rows * np + 3) / 4), (unsigned)nf);
+        k_pack_rows<<<grd, blk, 0, h->stream>>>(h->g, zf, np, pb);
         FL_CHECK_LAUNCH(h);
     }
     FL_CUDA(h, cudaEventRecord(h->ev_frame_packed, h->stream));

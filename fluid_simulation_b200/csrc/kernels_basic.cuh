@@ -35,6 +35,21 @@ __global__ void k_pack(Grid g, int zl_first, int nplanes, const float* __restric
     }
 }
 
+// Frame snapshot (simulation.cpp:140-148): up to five fields repacked to the reference layout in ONE launch.
+// One warp-row of threads per padded x-row (no integer divisions per element): blockDim = (64, 4),
+// grid = (ceil(rows * nplanes / 4), fields); reads and writes are both contiguous runs of W + 2 floats.
+struct PackBatch { const float* src[5]; float* dst[5]; };
+__global__ void __launch_bounds__(256) k_pack_rows(Grid g, int zl_first, int nplanes, PackBatch pb)
+{
+    const int r = blockIdx.x * blockDim.y + threadIdx.y;              // padded row index inside the packed planes
+    if (r >= g.rows * nplanes) return;
+    const int zl = zl_first + r / g.rows, y = r - (r / g.rows) * g.rows;
+    const int Wp = g.W + 2;
+    const float* __restrict__ s = pb.src[blockIdx.y] + fl_idx(g, 0, y, zl);
+    float* __restrict__ d = pb.dst[blockIdx.y] + (long long)r * Wp;
+    for (int x = threadIdx.x; x < Wp; x += blockDim.x) d[x] = s[x];
+}
+
 // ---- flag volume (once per obstacle upload) ---------------------------------------------------
 // Encodes exactly the obs tests the reference performs: `== 1.0f` for solid, `== 0.0f` plus the
 // 1..dim range test for "open" neighbours (simulation.cpp:222, 232-238, 307-312, 329-355).

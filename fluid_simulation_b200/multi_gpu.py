@@ -89,3 +89,21 @@ def reduce_stats(dist, st: dict) -> dict:
         vals = [p[k] for p in parts]
         out[k] = sum(vals) if k.endswith("_sum") else (min(vals) if k.endswith("_min") else max(vals))
     return out
+
+
+def gather_global_state(sim, dist, names=None) -> dict:
+    """Global padded fields on rank 0, merged from every rank's owned planes (other ranks get partial
+    sums they should ignore).  The owned planes are disjoint and everything else is all-zero bits, so an
+    INTEGER sum is a bitwise merge (a float sum would turn -0.0 into +0.0)."""
+    import numpy as np
+    import torch
+    st = sim.state()
+    out = {}
+    cuda = dist.get_backend() == "nccl"
+    for n in (names or list(st)):
+        t = torch.from_numpy(st[n].view(np.int32).copy())
+        if cuda:
+            t = t.cuda()
+        dist.reduce(t, 0, op=dist.ReduceOp.SUM)
+        out[n] = t.cpu().numpy().view(np.float32)
+    return out

@@ -307,16 +307,46 @@ class Simulation:
     def frame_wait(self):
         self._ck(self._L.fluid_frame_wait(self._h))
 
-    def open_frame_files(self, directory="data"):
-        """Open the reference's five output files (simulation.cpp:56-60)."""
-        os.makedirs(directory, exist_ok=True)
-        self._frame_files = [open(os.path.join(directory, n), "wb") for n in FRAME_FILES]
+    def _owned_planes(self):
+        """(first global padded plane, count) this rank owns in a frame: its interior planes plus the global
+        ghost plane(s) of the end slabs -- the planes fluid_dump_frame_async fills."""
+        first = 0 if self.rank == 0 else self.z_lo
+        last = self.depth + 1 if self.rank == self.nranks - 1 else self.z_lo + self.d_local - 1
+        return first, last - first + 1
+
+    def open_frame_files(self, directory="data", dist=None):
+        """Open the reference's five output files (simulation.cpp:56-60).  z-slabs (nranks > 1) share ONE set
+        of files: rank 0 creates and truncates them, every rank then writes only the planes it owns at their
+        offset inside each frame (`os.pwrite`), so the bytes equal the single-GPU / reference files.  That is a
+        collective and needs the process group (`dist`); without it a multi-rank handle refuses."""
+        if self.nranks > 1 and dist is None:
+            raise FluidError("open_frame_files: a z-slab handle (nranks > 1) needs the process group (dist=...): "
+                             "ranks share the frame files and must not truncate each other's frames")
+        self._frame_dist = dist if self.nranks > 1 else None
+        self._frames_written = 0
+        if self._frame_dist is None or self.rank == 0:
+            os.makedirs(directory, exist_ok=True)
+            self._frame_files = [open(os.path.join(directory, n), "wb") for n in FRAME_FILES]
+        if self._frame_dist is not None:
+            self._frame_dist.barrier()                   # the files exist and are empty
+            if self.rank != 0:
+                self._frame_files = [open(os.path.join(directory, n), "r+b") for n in FRAME_FILES]
 
     def flush_frames(self):
         if self._frame_files and getattr(self, "_frame_pending", False):
             self.frame_wait()
-            for f, (arr, _) in zip(self._frame_files, self._frame_bufs):
-                f.write(arr.tobytes())
+            if getattr(self, "_frame_dist", None) is None:
+                if self.nranks > 1:
+                    raise FluidError("flush_frames: multi-rank frame files were not opened with dist=")
+                for f, (arr, _) in zip(self._frame_files, self._frame_bufs):
+                    f.write(arr.tobytes())
+            else:
+                first, count = self._owned_planes()
+                plane_bytes = self.shape[1] * self.shape[2] * 4
+                off = self._frames_written * self.size * 4 + first * plane_bytes
+                for f, (arr, _) in zip(self._frame_files, self._frame_bufs):
+                    os.pwrite(f.fileno(), arr[first:first + count].tobytes(), off)
+            self._frames_written = getattr(self, "_frames_written", 0) + 1
             self._frame_pending = False
 
     # -- restart (SURVEY 8(f)-3): a dumped frame is a complete state ----------------------------
@@ -348,13 +378,28 @@ class Simulation:
             self.set(field, a.reshape(self.depth + 2, self.height + 2, self.width + 2))
         return k
 
-    def run(self, directory="data", dump_every=1, verbose=True):
+    def run(self, directory="data", dump_every=1, verbose=True, dist=None):
         """Simulation::run() (simulation.cpp:49-91): `iter` steps, frames appended to data/*.bin,
-        density sum every 100 steps and the final min/max statistics on stdout."""
+        density sum every 100 steps and the final min/max statistics on stdout.  z-slab handles (nranks > 1)
+        must pass the process group: frames go to shared files (see open_frame_files), statistics are reduced
+        over the ranks, rank 0 prints and writes meta.json."""
+        if self.nranks > 1 and dist is None:
+            raise FluidError("run(): a z-slab handle (nranks > 1) needs the process group (dist=...); "
+                             "per-rank runs would overwrite each other's frames and print per-slab statistics")
+        lead = self.rank == 0
+        verbose = verbose and lead
+
+        def stats():
+            st = self.stats()
+            if self.nranks > 1:
+                from . import multi_gpu
+                st = multi_gpu.reduce_stats(dist, st)
+            return st
+
         if verbose:
             print(f"starting 3-D simulation: {self.width}x{self.height}x{self.depth}  steps = {self.iter}")
         if directory is not None:
-            self.open_frame_files(directory)
+            self.open_frame_files(directory, dist)
         self._frame_pending = False
         for i in range(self.iter):
             self.run_iterations(1)
@@ -362,14 +407,19 @@ class Simulation:
                 self.flush_frames()              # write the previous frame while this step ran
                 self.dump_frame_async()
                 self._frame_pending = True
-            if verbose and (i + 1) % 100 == 0 and i > 0:
-                print(f"step {i + 1}\n  density sum = {self.stats()['dens_sum']:g}")
+            if (i + 1) % 100 == 0 and i > 0:
+                st = stats()                     # collective on z-slabs: every rank takes part
+                if verbose:
+                    print(f"step {i + 1}\n  density sum = {st['dens_sum']:g}")
         self.flush_frames()
         if directory is not None:
             for f in self._frame_files:
                 f.flush()
-            self.write_sidecar(directory, self.iter // dump_every, dump_every)
-        st = self.stats()
+            if self.nranks > 1:
+                dist.barrier()                   # every rank's planes are in the files
+            if lead:
+                self.write_sidecar(directory, self.iter // dump_every, dump_every)
+        st = stats()
         if verbose:
             print("\n--- statistics -------------------------------------------------")
             print(f"density  min = {st['dens_min']:g}\ndensity  max = {st['dens_max']:g}")

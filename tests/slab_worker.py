@@ -22,16 +22,7 @@ def main():
     from oracle import OracleSim, ORDER_RB, ORDER_JACOBI
 
     def gather_global(sim):
-        """global padded fields on rank 0 from every rank's owned planes"""
-        st = sim.state()        # global-shaped arrays, only owned planes filled
-        out = {}
-        for n in FIELD_NAMES:
-            # owned planes are disjoint and the rest is all-zero bits: an INTEGER sum is a bitwise merge
-            # (a float sum would turn -0.0 into +0.0)
-            t = torch.from_numpy(st[n].view(np.int32)).cuda()
-            dist.reduce(t, 0, op=dist.ReduceOp.SUM)
-            out[n] = t.cpu().numpy().view(np.float32)
-        return out
+        return multi_gpu.gather_global_state(sim, dist, FIELD_NAMES)
 
     failures = 0
     cases = [("rb", SOLVER_RB, ORDER_RB), ("jacobi", SOLVER_JACOBI, ORDER_JACOBI)]

@@ -19,7 +19,7 @@ def _ngpu():
         return 0
 
 
-@pytest.mark.parametrize("n", [2, 4])
+@pytest.mark.parametrize("n", [2, 4, 8])
 def test_slab_parity(n):
     if _ngpu() < n:
         pytest.skip(f"needs {n} GPUs")

@@ -100,3 +100,35 @@ def test_tiled_equals_simple_kernels_wide(name, flag, order):
     a.set("obs", obs); b.set("obs", obs)
     a.run_iterations(2); b.run_iterations(2)
     assert_bitwise(a.state(), b.state(), FIELD_NAMES, f"tiled vs simple, W=1024 [{name}]")
+
+
+@pytest.mark.parametrize("name,flag,order", SOLVERS)
+@pytest.mark.parametrize("d", [16, 40])
+def test_headline_plane_vs_oracle(name, flag, order, d):
+    """The 256 x 256 plane of BASELINE.json configs[2] against the CPU ORACLE (not against the repo's own
+    simple kernels): airfoil mask, acc = 10, two run() iterations, default segment plan (no FLUID_TILED_ZC),
+    so the balanced plan, the 4-field diffusion launch, the v <-> v_prev swap and the dependent launches of
+    the benchmarked kernel configuration meet the oracle bit for bit."""
+    from fluid_simulation_b200 import Simulation, masks
+    w, h, acc = 256, 256, 10
+    gpu = Simulation(w, h, d, 1, acc=acc, flags=flag)
+    cpu = OracleSim(w, h, d, acc=acc, order=order)
+    obs = masks.airfoil(w, h, d)
+    gpu.set("obs", obs); cpu.set("obs", obs)
+    gpu.run_iterations(2); cpu.run_iterations(2)
+    assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, f"256x256x{d} airfoil, 2 iterations [{name}]")
+
+
+def test_headline_grid_vs_oracle_full_depth():
+    """configs[2] at its FULL size (256^3, airfoil, red-black): one run() iteration at acc = 4 (the oracle's
+    single thread needs ~40 s for it).  This is the regime the benchmark runs in and no smaller case reaches:
+    148 CTAs, segments crossing column boundaries, z-ranges of ~130 planes in the 4-field launch."""
+    from fluid_simulation_b200 import Simulation, masks
+    w = h = d = 256
+    acc = 4
+    gpu = Simulation(w, h, d, 1, acc=acc, flags=0)
+    cpu = OracleSim(w, h, d, acc=acc, order=ORDER_RB)
+    obs = masks.airfoil(w, h, d)
+    gpu.set("obs", obs); cpu.set("obs", obs)
+    gpu.run_iterations(1); cpu.run_iterations(1)
+    assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, "256^3 airfoil, 1 iteration, acc 4 [rb]")
