@@ -42,6 +42,14 @@ __host__ __device__ __forceinline__ long long fl_idx(const Grid& g, int x, int y
     return (long long)FL_XOFF + x + (long long)y * g.pitch + (long long)zl * g.plane;
 }
 
+// the 7-point update of linearSolver (simulation.cpp:263-269); neighbour sum strictly left to
+// right: x+1, x-1, y+1, y-1, z+1, z-1
+__device__ __forceinline__ float fl_relax(float rhs, float a, float c_recip, float xp, float xm,
+                                          float yp, float ym, float zp, float zm)
+{
+    return (rhs + a * (((((xp + xm) + yp) + ym) + zp) + zm)) * c_recip;
+}
+
 // velocity component b in {1,2,3} masks solids and no-slip cells, scalars (b == 0) only solids
 __device__ __forceinline__ unsigned fl_zero_mask(int b) { return b == 0 ? FL_SOLID : (FL_SOLID | FL_NOSLIP); }
 

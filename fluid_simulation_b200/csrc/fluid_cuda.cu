@@ -4,6 +4,7 @@
 // There is no CPU path: without a usable CUDA device every entry point fails.
 #include "solver.cuh"
 #include "sweep_stream.cuh"
+#include "sweep_pair.cuh"
 #include "wavefront.cuh"
 #include "comm.cuh"
 #include "voxelize.cuh"

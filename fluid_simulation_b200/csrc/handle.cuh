@@ -24,6 +24,7 @@ struct fluid_handle {
     unsigned halo_seq = 0;           // sweeps whose halos went out through peer stores so far
     unsigned char* cflags = nullptr; // per-cell flag bytes, same pitched geometry as the fields
     bool flags_dirty = true;
+    unsigned long long flags_version = 0;   // bumped whenever the flag volume is rebuilt (derived tables follow it)
     float* staging = nullptr;        // (Dl+2)*(H+2)*(W+2) floats, reference layout, for up/download
     float* frame_staging[5] = {};    // lazily allocated, reference layout, for async frame dumps
     bool frame_in_flight = false;

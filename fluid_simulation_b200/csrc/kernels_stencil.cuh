@@ -6,14 +6,6 @@
 #pragma once
 #include "common.cuh"
 
-// the 7-point update of linearSolver (simulation.cpp:263-269); neighbour sum strictly left to
-// right: x+1, x-1, y+1, y-1, z+1, z-1
-__device__ __forceinline__ float fl_relax(float rhs, float a, float c_recip, float xp, float xm,
-                                          float yp, float ym, float zp, float zm)
-{
-    return (rhs + a * (((((xp + xm) + yp) + ym) + zp) + zm)) * c_recip;
-}
-
 struct Quad7 { float c[4], xm, xp, yp[4], ym[4], zp[4], zm[4]; };
 
 __device__ __forceinline__ void fl_load_quad7(const Grid& g, const float* __restrict__ f,

@@ -33,6 +33,7 @@ static inline int fl_rebuild_flags(fluid_handle* h)
                                                                  h->cflags - h->g.plane);
     FL_CHECK_LAUNCH(h);
     h->flags_dirty = false;
+    ++h->flags_version;
     return 0;
 }
 

@@ -1,0 +1,156 @@
+// sweep_pair.cuh -- host side of the temporally blocked sweep (two red-black sweeps per HBM pass,
+// sweep_pair_kernel.cuh): zero-bit volume, launch sequence of a solve.  One GPU, red-black,
+// 136 <= W <= 256, W % 8 == 0, H even; everything else stays with k_sweep_stream (one sweep per pass).
+#pragma once
+#include "sweep_pair_kernel.cuh"
+
+#define SP_SEGCOST 8                     // extra pipeline steps per segment (6 fill / drain + prologue)
+
+// One bit per cell: "setBounds zeroes this cell" for scalars ([0]: solid) and for velocity components
+// ([1]: solid or touching a solid), simulation.cpp:219-245.  Layout: one 16-bit word per (plane, row pair,
+// lane): bits 0-7 = cells 1 + 8*lane .. + 7 of row 2*pair, bits 8-15 = the same cells of row 2*pair + 1.
+// 2 x 2 MB at 256^3: the sweeps read them from L2 instead of 1 byte per cell from HBM.
+__global__ void __launch_bounds__(256) k_build_zbits(Grid g, const unsigned char* __restrict__ flags,
+                                                     unsigned short* __restrict__ z0, unsigned short* __restrict__ z1, int pairs)
+{
+    const long long n = (long long)(g.Dl + 2) * pairs * 32;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const int lane = (int)(t & 31);
+        const long long r = t >> 5;
+        const int pr = (int)(r % pairs), zl = (int)(r / pairs);
+        unsigned s0 = 0u, s1 = 0u;
+        if (zl >= 1 && zl <= g.Dl)
+            for (int k = 0; k < 2; ++k) {
+                const int y = 2 * pr + k;
+                if (y < 1 || y > g.H) continue;
+                for (int i = 0; i < 8; ++i) {
+                    const int x = 1 + 8 * lane + i;
+                    if (x > g.W) break;
+                    const unsigned f = flags[fl_idx(g, x, y, zl)];
+                    if (f & FL_SOLID) s0 |= 1u << (8 * k + i);
+                    if (f & (FL_SOLID | FL_NOSLIP)) s1 |= 1u << (8 * k + i);
+                }
+            }
+        z0[t] = (unsigned short)s0; z1[t] = (unsigned short)s1;
+    }
+}
+
+struct PairState {                       // hangs off StreamState::pair
+    unsigned short* zbits[2] = { nullptr, nullptr };
+    int pairs = 0;
+    unsigned long long flags_version = ~0ull;      // version of the flag volume the bits were built from
+};
+
+void sw_pair_release(StreamState* s)
+{
+    PairState* ps = (PairState*)s->pair;
+    if (!ps) return;
+    cudaFree(ps->zbits[0]); cudaFree(ps->zbits[1]);
+    delete ps;
+    s->pair = nullptr;
+}
+
+inline bool fl_pair_eligible(fluid_handle* h)
+{
+    const bool off = getenv("FLUID_NO_PAIR") != nullptr;             // read per solve: tests A/B it inside one process
+    const Grid& g = h->g;
+    if (off || h->nranks != 1 || (h->flags & FLUID_SOLVER_MASK) != FLUID_SOLVER_RB) return false;
+    return g.W > 128 && g.W <= 256 && (g.W & 7) == 0 && (g.H & 1) == 0 && g.cells < (1ll << 32);
+}
+
+template <int NP>
+inline int sw_pair_run(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
+                       unsigned x_from_rhs, int npairs)
+{
+    using GE = SpGeom<NP>;
+    const Grid& g = h->g;
+    StreamState* s = sw_state(h);
+    typedef void (*pair_kernel)(const PairArgs);
+    const pair_kernel kerns[2] = { k_sweep_pair<NP, true>, k_sweep_pair<NP, false> };
+    for (int i = 0; i < 2; ++i)
+        FL_CUDA(h, cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
+    if (nb > 4) return fl_fail(h, FLUID_E_ARG, "streaming solve: %d batched fields", nb);
+    SwPlan plan;
+    if (int e = sw_get_plan(h, nb, GE::TY, 1, 0, &plan, SP_SEGCOST)) return e;
+
+    // zero bits, rebuilt whenever the flag volume was
+    if (!s->pair) s->pair = new PairState();
+    PairState* ps = (PairState*)s->pair;
+    if (!ps->zbits[0]) {
+        ps->pairs = (g.rows + 1) / 2;
+        const size_t n = (size_t)(g.Dl + 2) * ps->pairs * 32 * sizeof(unsigned short);
+        FL_CUDA(h, cudaMalloc(&ps->zbits[0], n));
+        FL_CUDA(h, cudaMalloc(&ps->zbits[1], n));
+    }
+    if (ps->flags_version != h->flags_version) {
+        const long long n = (long long)(g.Dl + 2) * ps->pairs * 32;
+        k_build_zbits<<<fl_grid_1d(n), 256, 0, h->stream>>>(g, h->cflags, ps->zbits[0], ps->zbits[1], ps->pairs);
+        FL_CHECK_LAUNCH(h);
+        ps->flags_version = h->flags_version;
+    }
+
+    PairArgs A;
+    A.g = g; A.a = a; A.c_recip = 1.0f / c;                              // simulation.cpp:257
+    A.nty = (g.H + GE::TY - 1) / GE::TY;
+    A.segs = plan.segs; A.seg_first = plan.seg_first;
+    A.zbits[0] = ps->zbits[0]; A.zbits[1] = ps->zbits[1]; A.zb_pairs = ps->pairs;
+
+    float* cur[4]; float* alt[4];
+    if (nb == 4 && !h->scratch[3]) {                                      // fourth ping-pong partner, first use
+        const size_t fb = (size_t)g.cells * sizeof(float);
+        FL_CUDA(h, cudaMalloc(&h->scratch[3], fb));
+        FL_CUDA(h, cudaMemsetAsync(h->scratch[3], 0, fb, h->stream));
+        h->scratch[3] += g.plane;
+    }
+    for (int i = 0; i < nb; ++i) {
+        cur[i] = h->field[fid[i]]; alt[i] = h->scratch[i];
+        A.b[i] = b[i];
+        if (int e = sw_get_map(h, h->field[pid[i]], SW_RBOXW, GE::TR, &A.rmap[i])) return e;
+    }
+    dim3 ge((2 * (g.W + 2) + 2 * g.H + 127) / 128, g.Dl + 2);
+    for (int i = 0; i < nb; ++i) {                                        // edge/corner ghosts follow (see sw_run)
+        if ((x_from_rhs >> i) & 1u) {
+            k_copy_edges<<<ge, 128, 0, h->stream>>>(g, h->field[pid[i]], cur[i]);
+            FL_CHECK_LAUNCH(h);
+            k_copy_edges<<<ge, 128, 0, h->stream>>>(g, h->field[pid[i]], alt[i]);
+        } else
+            k_copy_edges<<<ge, 128, 0, h->stream>>>(g, cur[i], alt[i]);
+        FL_CHECK_LAUNCH(h);
+    }
+    for (int k = 0; k < npairs; ++k) {                                    // simulation.cpp:258, two iterations at a time
+        const unsigned from_rhs = k == 0 ? x_from_rhs : 0u;               // see sw_run
+        for (int i = 0; i < nb; ++i) {
+            const bool fr = (from_rhs >> i) & 1u;
+            if (int e = sw_get_map(h, fr ? h->field[pid[i]] : cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
+            A.dst[i] = fr ? cur[i] : alt[i];
+        }
+        const pair_kernel kern = kerns[(s->zigzag && (k & 1)) ? 1 : 0];   // odd passes stream the other way (L2 reuse)
+        if (s->pdl >= 1) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(plan.nctas); cfg.blockDim = dim3(GE::THREADS); cfg.dynamicSmemBytes = GE::SMEM; cfg.stream = h->stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            FL_CUDA(h, cudaLaunchKernelEx(&cfg, kern, A));
+        } else
+            kern<<<plan.nctas, GE::THREADS, GE::SMEM, h->stream>>>(A);
+        FL_CHECK_LAUNCH(h);
+        for (int i = 0; i < nb; ++i) if (!((from_rhs >> i) & 1u)) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
+    }
+    for (int i = 0; i < nb; ++i)
+        if (cur[i] != h->field[fid[i]]) { h->scratch[i] = h->field[fid[i]]; h->field[fid[i]] = cur[i]; }
+    return 0;
+}
+
+// the first 2 * floor(acc / 2) sweeps of a solve, two per pass; *done = sweeps performed
+int fl_pair_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
+                         unsigned x_from_rhs, int* done)
+{
+    *done = 0;
+    const int npairs = h->acc / 2;
+    if (npairs <= 0 || !fl_pair_eligible(h)) return 0;
+    if (int e = sw_pair_run<8>(h, nb, b, fid, pid, a, c, x_from_rhs, npairs)) return e;
+    *done = 2 * npairs;
+    return 0;
+}

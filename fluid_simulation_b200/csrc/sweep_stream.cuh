@@ -27,18 +27,10 @@
 #pragma once
 #include "handle.cuh"
 #include "kernels_stencil.cuh"
+#include "sweep_common.cuh"
 #include <cuda.h>
 #include <map>
 #include <cstdlib>
-
-#define SW_BOXW   136                    // floats per x box row: halo quad + 32 quads + halo quad
-#define SW_RBOXW  128                    // floats per rhs box row (no halo columns)
-#define SW_SMEM_MAX 232448               // 227 KB of dynamic shared memory per CTA on sm_100
-#define SW_SM_SMEM  233472               // 228 KB of shared memory per SM (each resident CTA also reserves 1 KB)
-
-// column (batched field * row tiles + row tile), planes za..zb; mode bit 0 = streamed downwards,
-// bits 1-2 = 1 + slab face (0 lower, 1 upper) whose two boundary planes this segment hands to the z-neighbour
-struct SwSeg { int col, za, zb, mode; };
 
 struct alignas(64) StreamArgs {
     CUtensorMap map[4];                  // source field of each batched solve (box SW_BOXW x BR x 1)
@@ -95,13 +87,22 @@ __device__ __forceinline__ void sw_tma_load_3d(void* dst, const CUtensorMap* map
         ::"r"(sw_smem(dst)), "l"(reinterpret_cast<unsigned long long>(map)), "r"(c0), "r"(c1), "r"(c2),
           "r"(sw_smem(bar)) : "memory");
 }
+__device__ __forceinline__ void sw_fence_mbar_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+// Programmatic dependent launch (no-ops unless the launch carries the attribute): the next sweep of the
+// solve may be scheduled while this one drains; no field data is touched before the kernel this one
+// depends on has completed and flushed.
+__device__ __forceinline__ void sw_grid_dep_sync()
+{
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
 __device__ __forceinline__ void sw_fence_proxy_async()
 {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
-// 128-bit shared load.  Where only two lanes of the quad are consumed the caller folds the other two
-// into a sink word (sw_lds4_half), otherwise the load is narrowed to two scalar LDS.
-__device__ __forceinline__ float4 sw_lds4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 // cell left of a quad (L) / right of it (R): the neighbour lane's outer cell by shuffle; the two
 // edge lanes of the warp read the halo column of the shared-memory box instead.
 __device__ __forceinline__ float sw_left(const float4& c, const float* row_quad, int lane)
@@ -116,7 +117,6 @@ __device__ __forceinline__ float sw_right(const float4& c, const float* row_quad
     if (lane == 31) R = row_quad[4];
     return R;
 }
-__device__ __forceinline__ void   sw_sts4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
 // relax the two lanes (E, E+2) of quad c in place.  L / R are the cells left of lane 0 / right of
 // lane 3; only the one that the colour needs is read.
@@ -133,43 +133,6 @@ __device__ __forceinline__ void sw_relax2(float4& c, float L, float R, const flo
         const float n1 = fl_relax(r.y, a, cr, c.z, c.x, yp.y, ym.y, zp.y, zm.y);
         const float n3 = fl_relax(r.w, a, cr, R,   c.z, yp.w, ym.w, zp.w, zm.w);
         c.y = n1; c.w = n3;
-    }
-}
-
-// edge bits of a thread's quad (which face ghosts its store also has to write)
-#define SW_XLO 1u
-#define SW_XHI 2u
-#define SW_YLO 4u
-#define SW_YHI 8u
-#define SW_ZLO 16u
-#define SW_ZHI 32u
-
-// the setBounds epilogue for one finished quad (simulation.cpp:183-246), see fl_store_bounded:
-// ghosts take the PRE-zero value, then solids (and, for velocity components, cells touching a
-// solid) are zeroed.
-__device__ __forceinline__ void sw_store(const Grid& g, float* __restrict__ out, long long c, const float4& raw,
-                                         unsigned f4, int b, unsigned zmask4, unsigned edge)
-{
-    const unsigned t = f4 & zmask4;
-    float4 v;
-    v.x = (t & 0x000000ffu) ? 0.0f : raw.x;
-    v.y = (t & 0x0000ff00u) ? 0.0f : raw.y;
-    v.z = (t & 0x00ff0000u) ? 0.0f : raw.z;
-    v.w = (t & 0xff000000u) ? 0.0f : raw.w;
-    st4(out + c, v);
-    if (edge) {
-        if (edge & SW_XLO) out[c - 1] = (b == 1) ? -raw.x : raw.x;            // :189
-        if (edge & SW_XHI) out[c + 4] = raw.w;                                // :191 outflow copy
-        if (edge & (SW_YLO | SW_YHI)) {                                       // :198-201
-            const float4 gy = (b == 2) ? make_float4(-raw.x, -raw.y, -raw.z, -raw.w) : raw;
-            if (edge & SW_YLO) st4(out + c - g.pitch, gy);
-            if (edge & SW_YHI) st4(out + c + g.pitch, gy);
-        }
-        if (edge & (SW_ZLO | SW_ZHI)) {                                       // :208-214
-            const float4 gz = (b == 3) ? make_float4(-raw.x, -raw.y, -raw.z, -raw.w) : raw;
-            if (edge & SW_ZLO) st4(out + c - g.plane, gz);
-            if (edge & SW_ZHI) st4(out + c + g.plane, gz);
-        }
     }
 }
 
@@ -596,6 +559,7 @@ struct StreamState {
     bool face_cta = true;                                       // separate edge CTAs (plan part 4); FLUID_SW_FACE_CTA=0: hand-over inside ordinary segments (part 5)
     int edge = SW_EDGE_DEFAULT;                                 // planes per edge segment at an interior slab face (>= 2)
     int plan_mode = 2, plan_min_fill = 85;
+    void* pair = nullptr;                                       // PairState (sweep_pair.cuh)
     int pdl = 1;                                                // FLUID_SW_PDL: programmatic dependent launch between the sweeps of a solve; 0 = off, 1 = on one GPU (measured: 22.78 -> 22.41 ms per 256^3 step), 2 = on z-slabs too                      // FLUID_SW_PLAN: 0 = auto, 1 = uniform ranges, 2 = balanced budget
 };
 
@@ -624,10 +588,15 @@ inline StreamState* sw_state(fluid_handle* h)
     return (StreamState*)h->tiled;
 }
 
+void sw_pair_release(StreamState* s);                              // sweep_pair.cuh
+int fl_pair_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
+                  unsigned x_from_rhs, int* done);
+
 inline void fl_tiled_release(fluid_handle* h)
 {
     StreamState* s = (StreamState*)h->tiled;
     if (s) for (auto& kv : s->plans) { cudaFree(kv.second.segs); cudaFree(kv.second.seg_first); }
+    if (s) sw_pair_release(s);
     delete s;
     h->tiled = nullptr;
 }
@@ -670,10 +639,10 @@ inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows
 // one grid, edge CTAs first, for the sweep that hands its halos over itself; part 5 = all planes as in
 // part 0, the segments that touch a slab face doing the hand-over on their way (FLUID_SW_FACE_CTA=0; as fast
 // with one face per rank, slower with two: 4 GPUs 30.2 vs 27.9 ms/step).
-inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPlan* out)
+inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPlan* out, int segcost = SW_SEGCOST)
 {
     StreamState* s = sw_state(h);
-    auto key = std::make_pair(nb, (ty * 16 + cps) * 4 + part);
+    auto key = std::make_pair(nb, ((ty * 16 + cps) * 8 + part) * 16 + segcost);
     auto it = s->plans.find(key);
     if (it == s->plans.end()) {
         const Grid& g = h->g;
@@ -716,7 +685,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
             // than the others and get that much less work
             const long long n_edge = (long long)ncol * ((lo_face ? 1 : 0) + (hi_face ? 1 : 0));
             const long long n_prompt = (part == 3 || part == 4) ? nc - n_edge % nc : nc;
-            const long long late = s->edge + SW_SEGCOST + 2;
+            const long long late = s->edge + segcost + 2;
             // Uniform plan: every column is cut into the same S ranges and one CTA streams range k of a
             // column, upwards for even k, downwards for odd k.  Neighbouring row tiles are then on the same
             // plane at the same time and the ranges of a column reach their shared boundary together, so
@@ -742,18 +711,18 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
                     long long left = budget - (k >= n_prompt ? late : 0);
                     while (c < ncol) {
                         const int rem = Dl - z;
-                        long long take = left - SW_SEGCOST < rem ? left - SW_SEGCOST : rem;
+                        long long take = left - segcost < rem ? left - segcost : rem;
                         if (rem - take > 0 && rem - take < SW_MINSEG) take = rem;       // no tiny leftovers
                         if (take < SW_MINSEG && take < rem) break;                      // no tiny starts
                         if (take <= 0) break;
                         if (emit) segs.push_back(SwSeg{ c, zoff + z + 1, zoff + z + (int)take, 0 });
-                        left -= take + SW_SEGCOST; z += (int)take;
+                        left -= take + segcost; z += (int)take;
                         if (z == Dl) { ++c; z = 0; }
                     }
                 }
                 return c == ncol;
             };
-            long long lo_b = T / nc, hi_b = T / nc + 3 * SW_SEGCOST + 2 * SW_MINSEG + Dl;
+            long long lo_b = T / nc, hi_b = T / nc + 3 * segcost + 2 * SW_MINSEG + Dl;
             while (!build(hi_b, false)) hi_b *= 2;
             while (lo_b + 1 < hi_b) {
                 const long long mid = (lo_b + hi_b) / 2;
@@ -793,7 +762,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
                 s2.insert(s2.end(), rest.begin(), rest.end());
             }
             f2.push_back((int)s2.size());
-            if (!ok) return sw_get_plan(h, nb, ty, cps, 4, out);                   // degenerate cut: separate edge CTAs
+            if (!ok) return sw_get_plan(h, nb, ty, cps, 4, out, segcost);                   // degenerate cut: separate edge CTAs
             segs.swap(s2); first.swap(f2);
         }
         SwPlan pl;
@@ -811,7 +780,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
 
 template <int TXW, int NP, int CPS>
 inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
-                  bool jacobi, unsigned x_from_rhs)
+                  bool jacobi, unsigned x_from_rhs, int nsweeps, int first_sweep = 0)
 {
     using GE = SwGeom<TXW, NP, CPS>;
     const Grid& g = h->g;
@@ -871,7 +840,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     // Single-field solves re-read the same right-hand side acc times: optionally pin it in the
     // persisting part of L2 (off by default, see fluid_create).
     const size_t fbytes = (size_t)g.cells * sizeof(float);
-    const bool pin = nb == 1 && h->l2_persist_max > 0 && h->acc > 1;
+    const bool pin = nb == 1 && h->l2_persist_max > 0 && nsweeps > 1;
     if (pin) {
         cudaStreamAttrValue av = {};
         av.accessPolicyWindow.base_ptr = (void*)h->field[pid[0]];
@@ -882,7 +851,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
         FL_CUDA(h, cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av));
     }
-    for (int k = 0; k < h->acc; ++k) {                                    // simulation.cpp:258
+    for (int k = 0; k < nsweeps; ++k) {                                   // simulation.cpp:258
         // x_from_rhs: the first sweep reads its guess from the right-hand-side buffer (same values: the caller
         // swapped the two fields instead of copying, simulation.cpp:108-110) and writes field[fid]
         const unsigned from_rhs = k == 0 ? x_from_rhs : 0u;                // per batched field
@@ -891,7 +860,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
             if (int e = sw_get_map(h, fr ? h->field[pid[i]] : cur[i], SW_BOXW, GE::BR, &A.map[i])) return e;
             A.dst[i] = fr ? cur[i] : alt[i];
         }
-        A.flip = (s->zigzag && (k & 1)) ? 1 : 0;         // odd sweeps stream the other way (L2 reuse)
+        A.flip = (s->zigzag && ((k + first_sweep) & 1)) ? 1 : 0;         // odd sweeps stream the other way (L2 reuse)
         const sweep_kernel kern = kerns[mixed ? 2 : A.flip];
         const unsigned seq = push ? ++h->halo_seq : 0u;
         if (fused) {
@@ -933,7 +902,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
             if (int e = fl_halo_exchange(h, nb, cur)) return e;
         }
     }
-    if (fused && h->acc > 0) if (int e = fl_halo_wait(h, h->stream, h->halo_seq)) return e;
+    if (fused && nsweeps > 0) if (int e = fl_halo_wait(h, h->stream, h->halo_seq)) return e;
     if (pin) {
         cudaStreamAttrValue av = {};
         av.accessPolicyWindow.num_bytes = 0;
@@ -984,15 +953,21 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
     const int ngroups = (s->unbatch && nb > 1) ? nb : 1, per = nb / ngroups;
     for (int gi = 0; gi < ngroups; ++gi) {
         const int* bb = b + gi * per; const int* ff = fid + gi * per; const int* pp = pid + gi * per;
-        int e;
-        if (g.W <= 128)      e = sw_run<1, 16, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
+        int e = 0, done = 0;
+        unsigned xfr = x_from_rhs;
+        // two sweeps per HBM pass where the temporally blocked kernel applies (sweep_pair.cuh); an odd
+        // sweep count ends with one ordinary sweep
+        if (!jac && per <= 4) { e = fl_pair_solve(h, per, bb, ff, pp, a, c, xfr, &done); if (e) return e; if (done) xfr = 0u; }
+        const int rest = h->acc - done;
+        if (rest <= 0) continue;
+        if (g.W <= 128)      e = sw_run<1, 16, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         else if (g.W <= 256) {
-            if (s->cfg == 1)      e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
-            else if (s->cfg == 2) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
-            else if (s->cfg == 3) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
-            else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
-        } else if (g.W <= 512) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);
-        else                   e = sw_run<8, 2, 1>(h, per, bb, ff, pp, a, c, jac, x_from_rhs);   // two owned rows: x re-read twice
+            if (s->cfg == 1)      e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+            else if (s->cfg == 2) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+            else if (s->cfg == 3) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+            else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+        } else if (g.W <= 512) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+        else                   e = sw_run<8, 2, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);   // two owned rows: x re-read twice
         if (e) return e;
     }
     *handled = true;
