@@ -58,7 +58,7 @@ inline bool fl_pair_eligible(fluid_handle* h)
     return g.W > 128 && g.W <= 256 && (g.W & 7) == 0 && (g.H & 1) == 0 && g.cells < (1ll << 32);
 }
 
-template <int NP>
+template <int NP, int NU>
 inline int sw_pair_run(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
                        unsigned x_from_rhs, int npairs)
 {
@@ -66,7 +66,7 @@ inline int sw_pair_run(fluid_handle* h, int nb, const int* b, const int* fid, co
     const Grid& g = h->g;
     StreamState* s = sw_state(h);
     typedef void (*pair_kernel)(const PairArgs);
-    const pair_kernel kerns[2] = { k_sweep_pair<NP, true>, k_sweep_pair<NP, false> };
+    const pair_kernel kerns[2] = { k_sweep_pair<NP, true, NU>, k_sweep_pair<NP, false, NU> };
     for (int i = 0; i < 2; ++i)
         FL_CUDA(h, cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GE::SMEM));
     if (nb > 4) return fl_fail(h, FLUID_E_ARG, "streaming solve: %d batched fields", nb);
@@ -150,7 +150,10 @@ int fl_pair_solve(fluid_handle* h, int nb, const int* b, const int* fid, const i
     *done = 0;
     const int npairs = h->acc / 2;
     if (npairs <= 0 || !fl_pair_eligible(h)) return 0;
-    if (int e = sw_pair_run<8>(h, nb, b, fid, pid, a, c, x_from_rhs, npairs)) return e;
+    // FLUID_PAIR_UNROLL=2: the two-step loop body with a ring rotation (a third of the code) instead of six
+    const char* u = getenv("FLUID_PAIR_UNROLL");
+    if (u && atoi(u) == 2) { if (int e = sw_pair_run<8, 2>(h, nb, b, fid, pid, a, c, x_from_rhs, npairs)) return e; }
+    else                   { if (int e = sw_pair_run<8, 6>(h, nb, b, fid, pid, a, c, x_from_rhs, npairs)) return e; }
     *done = 2 * npairs;
     return 0;
 }

@@ -38,9 +38,14 @@
 #include "sweep_stream.cuh"              // the PTX wrappers (mbarrier, TMA, dependent launch); the host build emulates them
 #endif
 
-#define SP_NX 3                          // x ring: planes p, p+1 (landing), p+2 (in flight)
-#define SP_NR 6                          // rhs ring (= mbarriers): planes p-3 .. p+2
+#define SP_NX 4                          // x ring: planes p, p+1, p+2 (landing), p+3 (in flight): TMA runs two steps ahead
+#define SP_NR (SP_NX + 2)                // rhs ring (= mbarriers): a plane's right-hand side is read at steps p and p+2
 #define SP_SROW 128                      // floats per compressed colour row (4 per lane)
+// The register ring: six planes in six fixed slots.  In unrolled step U the plane p+1-j (j = 0: the plane being
+// loaded, 1: plane p, ..., 5: plane p-4) lives in slot SP_SLOT(j, U), so advancing by one plane renames
+// registers instead of moving them; NU steps make one loop body (6: no moves at all; 2: the ring is
+// rotated by two slots at the end of the body -- a third of the code).
+#define SP_SLOT(j, U) (((j) - (U) + 12) % 6)
 
 template <int NP>
 struct SpGeom {
@@ -51,11 +56,13 @@ struct SpGeom {
     static constexpr int XSLOTF = 2 * BOXF;                          // two 136-wide boxes side by side
     static constexpr int RBOXF = SW_RBOXW * TR;
     static constexpr int RSLOTF = 2 * RBOXF;
-    static constexpr int SBUFF = (TR + 2) * SP_SROW;                 // one published colour plane (+2 edge rows)
+    static constexpr int SBUFF = TR * SP_SROW;                       // one published colour plane (the outer neighbour rows
+                                                                     // of the first / last thread row fall into the adjacent
+                                                                     // buffer or the pad row: never-used values)
     static constexpr int THREADS = 32 * NP;
     static constexpr int TX_BYTES = 2 * (SW_BOXW * BR + SW_RBOXW * TR) * 4;
-    static constexpr size_t SMEM = (size_t)(SP_NX * XSLOTF + SP_NR * RSLOTF + 6 * SBUFF) * sizeof(float);
-    static_assert(SMEM <= SW_SMEM_MAX, "pair-sweep tile too large for shared memory");
+    static constexpr size_t SMEM = (size_t)(SP_NX * XSLOTF + SP_NR * RSLOTF + 6 * SBUFF + SP_SROW) * sizeof(float);
+    static_assert(SMEM + 64 <= SW_SMEM_MAX, "pair-sweep tile too large for shared memory");
 };
 
 struct alignas(64) PairArgs {
@@ -133,9 +140,25 @@ struct SpThread {
     int smaxA, smaxB;                    // last stage that is still needed on the row (halo rows: fewer)
     bool lane_in;
     unsigned eA, eB;                     // x / y edge bits of the store epilogue
-    float xgA[4], xgB[4];                // x ghost beside the row, planes p .. p-3 (lane 0: x = 0, last lane: x = W+1)
-    unsigned fz[4];                      // zero bits of planes p .. p-3: row A in bits 0-7, row B in bits 8-15
+    // rings indexed like the plane ring (SP_SLOT): only the entries of planes p .. p-3 are live
+    float xgA[6], xgB[6];                // x ghost beside the row (lane 0: x = 0, last lane: x = W+1)
+    unsigned fz[6];                      // zero bits: row A in bits 0-7, row B in bits 8-15
+    bool lo_lane, hi_lane;               // lane 0 / the lane that holds x = W
+    float4 h1A, h1B, h3A, h3B;           // right-hand side of the cells stage 1 / stage 3 relax NEXT step (loaded with the other colour)
+    unsigned sink;                       // keeps the unused lanes of 128-bit shared loads alive (see sp_lds_half)
 };
+
+// 128-bit shared loads of an octet of which only the colour PE is consumed.  ptxas would narrow them to four
+// scalar LDS -- each an 8-way bank conflict across the warp (lane stride 32 B) -- so the unused lanes are
+// folded into a sink word (one LOP3 per load).
+template <int PE>
+__device__ __forceinline__ float4 sp_lds_half(const float* p, unsigned& sink)
+{
+    const float4 v0 = sw_lds4(p), v1 = sw_lds4(p + 4);
+    if (PE == 0) sink |= (__float_as_uint(v0.y) | __float_as_uint(v0.w)) | (__float_as_uint(v1.y) | __float_as_uint(v1.w));
+    else         sink |= (__float_as_uint(v0.x) | __float_as_uint(v0.z)) | (__float_as_uint(v1.x) | __float_as_uint(v1.z));
+    return sp_pick<PE>(v0, v1);
+}
 
 // ---- one half-sweep on one plane ------------------------------------------------------------------
 // S = stage, E = parity of the step, UP = planes streamed upwards in z.  c = the plane the stage acts on,
@@ -143,13 +166,15 @@ struct SpThread {
 // (natural layout), else the colour plane published by the previous stage one step ago.  spub: where this
 // stage publishes its colour (S < 3).  rslot: the plane's right-hand side.  k = ring position of the plane
 // (xg / fz index) = S.
-template <int S, int E, bool UP>
+template <int S, int U, bool UP>
 __device__ __forceinline__ void sp_stage(SpThread& t, const PairArgs& A, SpPlane& c, SpPlane& ahead, SpPlane& behind,
                                          const float* __restrict__ ynbr, float* __restrict__ spub,
-                                         const float* __restrict__ rslot, int b, int zg, bool in_window,
+                                         const float4& rA, const float4& rB, int b, int zg, bool in_window,
                                          float* __restrict__ out, unsigned oA, bool store_plane)
 {
+    constexpr int E = U & 1;                               // segments start on an even step (see sp_segment)
     constexpr int PA = E, PB = 1 - E;                      // active positions of row A / row B
+    constexpr int K = SP_SLOT(S + 1, U), K1 = SP_SLOT(2, U), K3 = SP_SLOT(4, U);   // ring slots of this plane, of planes p-1 / p-3
     const float a = A.a, cr = A.c_recip;
     const bool doA = in_window && t.intA && S <= t.smaxA, doB = in_window && t.intB && S <= t.smaxB;
     if (!doA && !doB) return;                              // warp-uniform
@@ -158,40 +183,38 @@ __device__ __forceinline__ void sp_stage(SpThread& t, const PairArgs& A, SpPlane
     // x neighbours across lanes: row A needs L when PA == 0, else R; row B the other one
     float LA = 0.0f, RA = 0.0f, LB = 0.0f, RB = 0.0f;
     if (PA == 0) {
-        LA = __shfl_up_sync(0xffffffffu, c.a1.w, 1);   if (t.lane == 0) LA = t.xgA[S];
-        RB = __shfl_down_sync(0xffffffffu, c.b0.x, 1); if (t.lane == t.last) RB = t.xgB[S];
+        LA = __shfl_up_sync(0xffffffffu, c.a1.w, 1);   LA = t.lo_lane ? t.xgA[K] : LA;
+        RB = __shfl_down_sync(0xffffffffu, c.b0.x, 1); RB = t.hi_lane ? t.xgB[K] : RB;
     } else {
-        RA = __shfl_down_sync(0xffffffffu, c.a0.x, 1); if (t.lane == t.last) RA = t.xgA[S];
-        LB = __shfl_up_sync(0xffffffffu, c.b1.w, 1);   if (t.lane == 0) LB = t.xgB[S];
+        RA = __shfl_down_sync(0xffffffffu, c.a0.x, 1); RA = t.hi_lane ? t.xgA[K] : RA;
+        LB = __shfl_up_sync(0xffffffffu, c.b1.w, 1);   LB = t.lo_lane ? t.xgB[K] : LB;
     }
     float4 nA = make_float4(0.0f, 0.0f, 0.0f, 0.0f), nB = nA;
     if (doA) {
         float4 ym;
-        if (S == 0) ym = sp_pick<PA>(sw_lds4(ynbr + t.offA - SW_BOXW), sw_lds4(ynbr + t.offA - SW_BOXW + 4));
+        if (S == 0) ym = sp_lds_half<PA>(ynbr + t.offA - SW_BOXW, t.sink);
         else        ym = sw_lds4(ynbr + t.sA - SP_SROW);
-        const float4 r = sp_pick<PA>(sw_lds4(rslot + t.roffA), sw_lds4(rslot + t.roffA + 4));
         nA = sp_relax<PA>(c.a0, c.a1, LA, RA, sp_pick<PA>(c.b0, c.b1), ym, sp_pick<PA>(zpP.a0, zpP.a1),
-                          sp_pick<PA>(zmP.a0, zmP.a1), r, a, cr);
+                          sp_pick<PA>(zmP.a0, zmP.a1), rA, a, cr);
     }
     if (doB) {
         float4 yp;
-        if (S == 0) yp = sp_pick<PB>(sw_lds4(ynbr + t.offA + 2 * SW_BOXW), sw_lds4(ynbr + t.offA + 2 * SW_BOXW + 4));
+        if (S == 0) yp = sp_lds_half<PB>(ynbr + t.offA + 2 * SW_BOXW, t.sink);
         else        yp = sw_lds4(ynbr + t.sA + 2 * SP_SROW);
-        const float4 r = sp_pick<PB>(sw_lds4(rslot + t.roffA + SW_RBOXW), sw_lds4(rslot + t.roffA + SW_RBOXW + 4));
         nB = sp_relax<PB>(c.b0, c.b1, LB, RB, yp, sp_pick<PB>(c.a0, c.a1), sp_pick<PB>(zpP.b0, zpP.b1),
-                          sp_pick<PB>(zmP.b0, zmP.b1), r, a, cr);
+                          sp_pick<PB>(zmP.b0, zmP.b1), rB, a, cr);
     }
     // both rows were relaxed from the values before this stage; now they take their new values
     if (S < 2) {
         // ---- sweep 1: what setBounds will make of the ghosts next to these cells (simulation.cpp:187-215),
         // from the PRE-zero values; each ghost is read only by the cell it mirrors ----------------------
         if (doA) {
-            if (PA == 0) { if (t.lane == 0) t.xgA[S] = (b == 1) ? -nA.x : nA.x; }        // x = 0      :189
-            else         { if (t.lane == t.last) t.xgA[S] = nA.w; }                      // x = W + 1  :191
+            if (PA == 0) t.xgA[K] = t.lo_lane ? ((b == 1) ? -nA.x : nA.x) : t.xgA[K];    // x = 0      :189
+            else         t.xgA[K] = t.hi_lane ? nA.w : t.xgA[K];                         // x = W + 1  :191
         }
         if (doB) {
-            if (PB == 0) { if (t.lane == 0) t.xgB[S] = (b == 1) ? -nB.x : nB.x; }
-            else         { if (t.lane == t.last) t.xgB[S] = nB.w; }
+            if (PB == 0) t.xgB[K] = t.lo_lane ? ((b == 1) ? -nB.x : nB.x) : t.xgB[K];
+            else         t.xgB[K] = t.hi_lane ? nB.w : t.xgB[K];
         }
         if (t.ghostA && doB) sp_put<PB>(c.a0, c.a1, b == 2 ? sp_neg(nB) : nB);           // y = 0      :198
         if (t.ghostB && doA) sp_put<PA>(c.b0, c.b1, b == 2 ? sp_neg(nA) : nA);           // y = H + 1  :200
@@ -207,8 +230,8 @@ __device__ __forceinline__ void sp_stage(SpThread& t, const PairArgs& A, SpPlane
     if (S == 1) {
         // sweep 1 is complete on this plane: solids (and, for velocity components, cells that touch one)
         // become 0 (:219-245).  Only colour 1 needs it: the colour-0 values of sweep 1 are not read again.
-        nA = sp_zero<PA>(nA, t.fz[1]);
-        nB = sp_zero<PB>(nB, t.fz[1] >> 8);
+        nA = sp_zero<PA>(nA, t.fz[K1]);
+        nB = sp_zero<PB>(nB, t.fz[K1] >> 8);
     }
     if (doA) sp_put<PA>(c.a0, c.a1, nA);
     if (doB) sp_put<PB>(c.b0, c.b1, nB);
@@ -221,14 +244,14 @@ __device__ __forceinline__ void sp_stage(SpThread& t, const PairArgs& A, SpPlane
         const unsigned zbits = (zg == 1 ? SW_ZLO : 0u) | (zg == g.D ? SW_ZHI : 0u);
         const unsigned zmask4 = 0x01010101u;               // the bits below are already class-selected
         if (t.ownA && t.lane_in) {
-            const unsigned f = t.fz[3];
+            const unsigned f = t.fz[K3];
             const unsigned lo = (f & 1u) | ((f & 2u) << 7) | ((f & 4u) << 14) | ((f & 8u) << 21);
             const unsigned hi = ((f >> 4) & 1u) | ((f & 0x20u) << 3) | ((f & 0x40u) << 10) | ((f & 0x80u) << 17);
             sw_store(g, out, oA, c.a0, lo, b, zmask4, (t.eA & ~SW_XHI) | zbits);
             sw_store(g, out, oA + 4, c.a1, hi, b, zmask4, (t.eA & ~SW_XLO) | zbits);
         }
         if (t.ownB && t.lane_in) {
-            const unsigned f = t.fz[3] >> 8;
+            const unsigned f = t.fz[K3] >> 8;
             const unsigned lo = (f & 1u) | ((f & 2u) << 7) | ((f & 4u) << 14) | ((f & 8u) << 21);
             const unsigned hi = ((f >> 4) & 1u) | ((f & 0x20u) << 3) | ((f & 0x40u) << 10) | ((f & 0x80u) << 17);
             sw_store(g, out, oA + g.pitch, c.b0, lo, b, zmask4, (t.eB & ~SW_XHI) | zbits);
@@ -243,7 +266,7 @@ struct SpRing {                         // TMA ring position, runs on from segme
     int xs_con, rs_con; unsigned ph_con; // ... of the next plane consumed, and its mbarrier parity
 };
 
-template <int NP, bool UP>
+template <int NP, bool UP, int NU>
 __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, SpThread& t, float* const xring,
                                            float* const rring, float* const sbuf, unsigned long long* const bars,
                                            SpRing& R, const int tid, const int w)
@@ -263,10 +286,13 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
     const int wlo0 = max(za - 3, 1), whi0 = min(zb + 3, g.D);
     const int wlo1 = max(za - 2, 1), whi1 = min(zb + 2, g.D);
     const int wlo2 = max(za - 1, 1), whi2 = min(zb + 1, g.D);
-    const int ps = UP ? wlo0 : whi0;                             // first stage-0 plane
+    // first stage-0 plane; the unrolled body fixes the parity of a step by its position, so a segment whose
+    // first plane has the odd parity starts one (idle) step earlier: every window excludes that plane
+    const int ps0 = UP ? wlo0 : whi0;
+    const int ps = ((g.zlo + ps0) & 1) ? ps0 - DIR : ps0;
     const int pe = UP ? zb + 3 : za - 3;                         // plane index of the last step (stage 3 on zb / za)
     const int nsteps = (pe - ps) * DIR + 1;
-    const int first = ps - DIR;                                  // first plane loaded (0 .. D+1 on one GPU)
+    const int first = ps - DIR;                                  // first plane loaded (-1 .. D+2: inside the allocation)
     const int lastp = UP ? min(zb + 4, g.D + 1) : max(za - 4, 0);
     const int nplanes = (lastp - first) * DIR + 1;
 
@@ -307,12 +333,11 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
     const bool zb_ok = yA >= 0 && yA <= g.H;
 
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    SpPlane N, C0, C1, C2, C3, C4;
-    N.a0 = N.a1 = N.b0 = N.b1 = zero4; C0 = N; C1 = N; C2 = N; C3 = N; C4 = N;
+    SpPlane P[6];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { t.xgA[i] = 0.0f; t.xgB[i] = 0.0f; t.fz[i] = 0u; }
+    for (int i = 0; i < 6; ++i) { P[i].a0 = P[i].a1 = P[i].b0 = P[i].b1 = zero4; t.xgA[i] = 0.0f; t.xgB[i] = 0.0f; t.fz[i] = 0u; }
 
-    // slot bookkeeping: rs0 = rhs slot of plane p (stage s reads slot rs0 - s), xs0 = x slot of plane p
+    // slot bookkeeping: xs_p = x slot of plane p; rs0 / rs1 / rs2 = rhs slots of planes p, p-1, p-2
     auto consume = [&](const float*& xs, int& rs) {              // wait for the next plane in stream order
         sw_mbar_wait(&bars[R.rs_con], R.ph_con);
         xs = xring + R.xs_con * XSLOTF; rs = R.rs_con;
@@ -323,49 +348,81 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
         P.a0 = sw_lds4(xs + t.offA);           P.a1 = sw_lds4(xs + t.offA + 4);
         P.b0 = sw_lds4(xs + t.offA + SW_BOXW); P.b1 = sw_lds4(xs + t.offA + SW_BOXW + 4);
     };
-    const float* xs_p; int rs0;
-    { const float* xb; int rb; consume(xb, rb); load_plane(C1, xb); }        // the plane behind ps
-    consume(xs_p, rs0); load_plane(C0, xs_p);                                // plane ps
+    const float* xs_p; int rs0, rs1, rs2;
+    { const float* xb; int rb; consume(xb, rb); load_plane(P[SP_SLOT(2, 0)], xb); }   // the plane behind ps
+    consume(xs_p, rs0); load_plane(P[SP_SLOT(1, 0)], xs_p);                           // plane ps
+    rs1 = rs2 = rs0;
+    t.h1A = t.h1B = t.h3A = t.h3B = zero4;
     __syncthreads();        // the slot of the plane behind ps is re-armed by the first step
 
+    const bool edge_lane = t.lo_lane || t.hi_lane;
+    const int xg_off = t.offA + (t.lo_lane ? -1 : 8);            // the x ghost beside row A in an x slot
     int p = ps, jc = 1;                                          // jc = stream index of plane p
-    // one pipeline step with static parity EE = (z_global(p) + 1) & 1; the published colour planes are
-    // double-buffered by that parity (written [EE], read [1 - EE])
-#define SP_STEP(EE)                                                                                             \
+    // One pipeline step at unroll position U (parity U & 1 = (z_global(p) + 1) & 1); the published colour
+    // planes are double-buffered by that parity (written [E], read [1 - E]).  The right-hand side of a plane is
+    // read twice, as whole octets: at step p (colour 0 of sweep 1 now, the other colour kept for stage 1 of the
+    // next step) and at step p+2 (the same for sweep 2), so every lane of every 128-bit load is used.
+#define SP_STEP(U)                                                                                              \
     {                                                                                                           \
+        constexpr int EE = (U) & 1;                                                                             \
+        SpPlane& N = P[SP_SLOT(0, U)]; SpPlane& C0 = P[SP_SLOT(1, U)]; SpPlane& C1 = P[SP_SLOT(2, U)];          \
+        SpPlane& C2 = P[SP_SLOT(3, U)]; SpPlane& C3 = P[SP_SLOT(4, U)]; SpPlane& C4 = P[SP_SLOT(5, U)];         \
         if (issued < nplanes && issued - jc < SP_NX) { issue(first + DIR * issued); ++issued; }                 \
         const bool has_next = jc + 1 < nplanes;                                                                 \
         const float* xs_n = xs_p; int rs_n = rs0 + 1 == SP_NR ? 0 : rs0 + 1;    /* the ring position moves on even past the last plane */ \
         if (has_next) { consume(xs_n, rs_n); load_plane(N, xs_n); }                                             \
         /* x ghosts beside plane p as the last setBounds left them, and the plane's zero bits */               \
-        t.xgA[0] = xs_p[t.offA + (t.lane == 0 ? -1 : 8)];                                                       \
-        t.xgB[0] = xs_p[t.offA + SW_BOXW + (t.lane == 0 ? -1 : 8)];                                             \
-        t.fz[0] = (zb_ok && p >= 1 && p <= g.D) ? (unsigned)zbv[(unsigned)p * (unsigned)(A.zb_pairs * 32) + zb_row] : 0u; \
+        t.xgA[SP_SLOT(1, U)] = edge_lane ? xs_p[xg_off] : 0.0f;                                                 \
+        t.xgB[SP_SLOT(1, U)] = edge_lane ? xs_p[xg_off + SW_BOXW] : 0.0f;                                       \
+        t.fz[SP_SLOT(1, U)] = (zb_ok && p >= 1 && p <= g.D) ? (unsigned)zbv[(unsigned)p * (unsigned)(A.zb_pairs * 32) + zb_row] : 0u; \
         const int zg = g.zlo + p - 1;                                                                           \
-        float* const S0w = sbuf + (0 + (EE)) * SBUFF;     const float* const S0r = sbuf + (0 + 1 - (EE)) * SBUFF; \
-        float* const S1w = sbuf + (2 + (EE)) * SBUFF;     const float* const S1r = sbuf + (2 + 1 - (EE)) * SBUFF; \
-        float* const S2w = sbuf + (4 + (EE)) * SBUFF;     const float* const S2r = sbuf + (4 + 1 - (EE)) * SBUFF; \
+        float* const S0w = sbuf + (0 + EE) * SBUFF;     const float* const S0r = sbuf + (0 + 1 - EE) * SBUFF;   \
+        float* const S1w = sbuf + (2 + EE) * SBUFF;     const float* const S1r = sbuf + (2 + 1 - EE) * SBUFF;   \
+        float* const S2w = sbuf + (4 + EE) * SBUFF;     const float* const S2r = sbuf + (4 + 1 - EE) * SBUFF;   \
         const int q1 = p - DIR, q2 = p - 2 * DIR, q3 = p - 3 * DIR;                                             \
-        sp_stage<0, EE, UP>(t, A, C0, N, C1, xs_p, S0w, rring + rs0 * RSLOTF, b, zg,                            \
-                            p >= wlo0 && p <= whi0, out, 0u, false);                                            \
-        sp_stage<1, EE, UP>(t, A, C1, C0, C2, S0r, S1w, rring + ((rs0 + SP_NR - 1) % SP_NR) * RSLOTF, b, zg - DIR, \
-                            q1 >= wlo1 && q1 <= whi1, out, 0u, false);                                          \
-        sp_stage<2, EE, UP>(t, A, C2, C1, C3, S1r, S2w, rring + ((rs0 + SP_NR - 2) % SP_NR) * RSLOTF, b, zg - 2 * DIR, \
-                            q2 >= wlo2 && q2 <= whi2, out, 0u, false);                                          \
-        sp_stage<3, EE, UP>(t, A, C3, C2, C4, S2r, nullptr, rring + ((rs0 + SP_NR - 3) % SP_NR) * RSLOTF, b, zg - 3 * DIR, \
-                            q3 >= za && q3 <= zb, out, oA0 + (unsigned)q3 * plane, true);                       \
-        C4 = C3; C3 = C2; C2 = C1; C1 = C0; C0 = N;                                                             \
-        t.xgA[3] = t.xgA[2]; t.xgA[2] = t.xgA[1]; t.xgA[1] = t.xgA[0];                                          \
-        t.xgB[3] = t.xgB[2]; t.xgB[2] = t.xgB[1]; t.xgB[1] = t.xgB[0];                                          \
-        t.fz[3] = t.fz[2]; t.fz[2] = t.fz[1]; t.fz[1] = t.fz[0];                                                \
-        xs_p = xs_n; rs0 = rs_n; p += DIR; ++jc;                                                                \
+        {                                                                                                       \
+            const float* rp = rring + rs0 * RSLOTF + t.roffA;                                                   \
+            const float4 u0 = sw_lds4(rp), u1 = sw_lds4(rp + 4), u2 = sw_lds4(rp + SW_RBOXW), u3 = sw_lds4(rp + SW_RBOXW + 4); \
+            sp_stage<0, U, UP>(t, A, C0, N, C1, xs_p, S0w, sp_pick<EE>(u0, u1), sp_pick<1 - EE>(u2, u3), b, zg, \
+                               p >= wlo0 && p <= whi0, out, 0u, false);                                         \
+            sp_stage<1, U, UP>(t, A, C1, C0, C2, S0r, S1w, t.h1A, t.h1B, b, zg - DIR,                           \
+                               q1 >= wlo1 && q1 <= whi1, out, 0u, false);                                       \
+            t.h1A = sp_pick<1 - EE>(u0, u1); t.h1B = sp_pick<EE>(u2, u3);                                       \
+        }                                                                                                       \
+        {                                                                                                       \
+            const float* rp = rring + rs2 * RSLOTF + t.roffA;                                                   \
+            const float4 u0 = sw_lds4(rp), u1 = sw_lds4(rp + 4), u2 = sw_lds4(rp + SW_RBOXW), u3 = sw_lds4(rp + SW_RBOXW + 4); \
+            sp_stage<2, U, UP>(t, A, C2, C1, C3, S1r, S2w, sp_pick<EE>(u0, u1), sp_pick<1 - EE>(u2, u3), b, zg - 2 * DIR, \
+                               q2 >= wlo2 && q2 <= whi2, out, 0u, false);                                       \
+            sp_stage<3, U, UP>(t, A, C3, C2, C4, S2r, nullptr, t.h3A, t.h3B, b, zg - 3 * DIR,                   \
+                               q3 >= za && q3 <= zb, out, oA0 + (unsigned)q3 * plane, true);                    \
+            t.h3A = sp_pick<1 - EE>(u0, u1); t.h3B = sp_pick<EE>(u2, u3);                                       \
+        }                                                                                                       \
+        xs_p = xs_n; rs2 = rs1; rs1 = rs0; rs0 = rs_n; p += DIR; ++jc;                                          \
         __syncthreads();                                                                                        \
     }
     int step = 0;
-    if (((g.zlo + ps) & 1) == 0) {                               // EE of the first step = (zg + 1) & 1 with zg = zlo + ps - 1
-        for (;;) { if (step++ == nsteps) break; SP_STEP(0) if (step++ == nsteps) break; SP_STEP(1) }
-    } else {
-        for (;;) { if (step++ == nsteps) break; SP_STEP(1) if (step++ == nsteps) break; SP_STEP(0) }
+    for (;;) {
+        if (step++ == nsteps) break;
+        SP_STEP(0)
+        if (step++ == nsteps) break;
+        SP_STEP(1)
+        if constexpr (NU == 6) {
+            if (step++ == nsteps) break;
+            SP_STEP(2)
+            if (step++ == nsteps) break;
+            SP_STEP(3)
+            if (step++ == nsteps) break;
+            SP_STEP(4)
+            if (step++ == nsteps) break;
+            SP_STEP(5)
+        } else {   // two steps done: rotate the rings by two slots so that the body starts at position 0 again
+            SpPlane Q[6]; float qa[6], qb[6]; unsigned qf[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) { Q[i] = P[i]; qa[i] = t.xgA[i]; qb[i] = t.xgB[i]; qf[i] = t.fz[i]; }
+#pragma unroll
+            for (int i = 0; i < 6; ++i) { P[i] = Q[(i + 4) % 6]; t.xgA[i] = qa[(i + 4) % 6]; t.xgB[i] = qb[(i + 4) % 6]; t.fz[i] = qf[(i + 4) % 6]; }
+        }
     }
 #undef SP_STEP
 }
@@ -373,7 +430,7 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
 // One launch = two red-black sweeps of up to four batched fields.  A CTA works through a short list of
 // segments (column = batched field x row tile, planes za .. zb).  sp_cta is the whole CTA program; the
 // kernel below hands it the shared memory (the host emulation calls it from one host thread per CUDA thread).
-template <int NP, bool UP>
+template <int NP, bool UP, int NU>
 __device__ __forceinline__ void sp_cta(const PairArgs& A, float* const sw_mem, unsigned long long* const bars,
                                        const int tid, const int bid)
 {
@@ -395,19 +452,21 @@ __device__ __forceinline__ void sp_cta(const PairArgs& A, float* const sw_mem, u
     t.lane_in = lane <= t.last;
     t.offA = (lane >> 4) * GE::BOXF + (1 + 2 * w) * SW_BOXW + 4 + 8 * (lane & 15);
     t.roffA = (lane >> 4) * GE::RBOXF + (2 * w) * SW_RBOXW + 8 * (lane & 15);
-    t.sA = (2 * w + 1) * SP_SROW + 4 * lane;
+    t.sA = (2 * w) * SP_SROW + 4 * lane;
+    t.lo_lane = lane == 0; t.hi_lane = lane == t.last; t.sink = 0u;
 
     SpRing R; R.xs_iss = R.rs_iss = R.xs_con = R.rs_con = 0; R.ph_con = 0u;
     for (int si = A.seg_first[bid]; si < A.seg_first[bid + 1]; ++si)
-        sp_segment<NP, UP>(A, A.segs[si], t, xring, rring, sbuf, bars, R, tid, w);
+        sp_segment<NP, UP, NU>(A, A.segs[si], t, xring, rring, sbuf, bars, R, tid, w);
+    if (A.nty < 0) A.dst[0][0] = __uint_as_float(t.sink);            // never taken: keeps t.sink observable
 }
 
 #ifndef SP_HOST_EMUL
-template <int NP, bool UP>
+template <int NP, bool UP, int NU>
 __global__ void __launch_bounds__(32 * NP, 1) k_sweep_pair(const __grid_constant__ PairArgs A)
 {
     extern __shared__ __align__(128) float sw_mem[];
     __shared__ unsigned long long bars[SP_NR];
-    sp_cta<NP, UP>(A, sw_mem, bars, (int)threadIdx.x, (int)blockIdx.x);
+    sp_cta<NP, UP, NU>(A, sw_mem, bars, (int)threadIdx.x, (int)blockIdx.x);
 }
 #endif

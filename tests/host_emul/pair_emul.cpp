@@ -39,6 +39,8 @@ struct EmulCta {
 static thread_local EmulCta* t_cta = nullptr;
 static thread_local int t_tid = 0;
 
+static inline unsigned __float_as_uint(float f) { unsigned u; memcpy(&u, &f, 4); return u; }
+static inline float __uint_as_float(unsigned u) { float f; memcpy(&f, &u, 4); return f; }
 static inline void __syncthreads() { t_cta->cta_bar.arrive_and_wait(); }
 static inline float emul_shfl(float v, int src_delta)
 {
@@ -99,7 +101,7 @@ static Grid make_grid(int w, int h, int d)
     return g;
 }
 
-template <bool UP>
+template <bool UP, int NU>
 static void run_cta(const PairArgs& A, int bid)
 {
     using GE = SpGeom<8>;
@@ -109,7 +111,7 @@ static void run_cta(const PairArgs& A, int bid)
     unsigned long long bars[SP_NR];
     std::vector<std::thread> th;
     for (int t = 0; t < GE::THREADS; ++t)
-        th.emplace_back([&, t]() { t_cta = &cta; t_tid = t; sp_cta<8, UP>(A, sm, bars, t, bid); });
+        th.emplace_back([&, t]() { t_cta = &cta; t_tid = t; sp_cta<8, UP, NU>(A, sm, bars, t, bid); });
     for (auto& x : th) x.join();
 }
 
@@ -117,7 +119,7 @@ static void run_cta(const PairArgs& A, int bid)
 // layout ((d+2) x (h+2) x (w+2)); segments are columns cut into chunks of `zchunk` planes, two segments per
 // CTA where possible (so that the ring runs on across segments).  Returns 0, or a negative error.
 extern "C" int pair_emul_sweep(int w, int h, int d, const float* x, const float* rhs, const float* obs, int b,
-                               float a, float c, int zchunk, int up, float* out)
+                               float a, float c, int zchunk, int up, int unroll, float* out)
 {
     using GE = SpGeom<8>;
     if (w <= 128 || w > 256 || (w & 7) || (h & 1)) return -1;
@@ -166,7 +168,8 @@ extern "C" int pair_emul_sweep(int w, int h, int d, const float* x, const float*
     A.map[0] = CUtensorMap{ fx.data(), { g.pitch, g.rows, g.Dl + 4 }, { g.pitch, g.plane }, { SW_BOXW, GE::BR } };
     A.rmap[0] = CUtensorMap{ fr.data(), { g.pitch, g.rows, g.Dl + 4 }, { g.pitch, g.plane }, { SW_RBOXW, GE::TR } };
     for (int bid = 0; bid + 1 < (int)first.size(); ++bid) {
-        if (up) run_cta<true>(A, bid); else run_cta<false>(A, bid);
+        if (unroll == 6) { if (up) run_cta<true, 6>(A, bid); else run_cta<false, 6>(A, bid); }
+        else             { if (up) run_cta<true, 2>(A, bid); else run_cta<false, 2>(A, bid); }
     }
     for (int z = 0; z <= d + 1; ++z) for (int y = 0; y <= h + 1; ++y) for (int xx = 0; xx <= w + 1; ++xx)
         out[((size_t)z * g.rows + y) * Wp + xx] = fo[(size_t)g.plane + fl_idx(g, xx, y, z)];
