@@ -79,8 +79,8 @@ int fluid_ipc_export(fluid_handle* h, int alloc_id, char out[64])
         return fl_fail(h, FLUID_E_ARG, "fluid_ipc_export: bad allocation id %d", alloc_id);
     // a field id names the buffer the field lives in right now (the solver permutes them)
     void* base = alloc_id == FLUID_IPC_SYNC ? (void*)h->d_sync
-               : alloc_id >= FLUID_IPC_SCRATCH0 ? (void*)(h->scratch[alloc_id - FLUID_IPC_SCRATCH0] - h->g.plane)
-               : (void*)(h->field[alloc_id] - h->g.plane);
+               : alloc_id >= FLUID_IPC_SCRATCH0 ? (void*)(h->scratch[alloc_id - FLUID_IPC_SCRATCH0] - FL_ZPAD * h->g.plane)
+               : (void*)(h->field[alloc_id] - FL_ZPAD * h->g.plane);
     cudaIpcMemHandle_t mh;
     FL_CUDA(h, cudaIpcGetMemHandle(&mh, base));
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");
@@ -105,10 +105,10 @@ int fluid_ipc_import(fluid_handle* h, int peer_rank, int alloc_id, const char in
     int slot = alloc_id;
     if (alloc_id < FLUID_NFIELDS)
         for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
-            if (h->alloc_base[i] == h->field[alloc_id] - h->g.plane) slot = i;
+            if (h->alloc_base[i] == h->field[alloc_id] - FL_ZPAD * h->g.plane) slot = i;
     if (alloc_id >= FLUID_IPC_SCRATCH0 && alloc_id < FLUID_IPC_SYNC)
         for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
-            if (h->alloc_base[i] == h->scratch[alloc_id - FLUID_IPC_SCRATCH0] - h->g.plane) slot = i;
+            if (h->alloc_base[i] == h->scratch[alloc_id - FLUID_IPC_SCRATCH0] - FL_ZPAD * h->g.plane) slot = i;
     c->peer_alloc[peer_rank][slot] = (float*)p;
     return 0;
 }

@@ -62,13 +62,14 @@ static inline void fl_slab_of(int d, int nranks, int r, int* zlo, int* dl)
     *zlo = 1 + r * base + (r < rem ? r : rem);
 }
 
-// Send my planes {1,2} down and {Dl-1,Dl} up, receive the neighbours' into {Dl+1,Dl+2} / {-1,0}.
+// Send my planes 1 .. FL_HALO down and Dl-FL_HALO+1 .. Dl up, receive the neighbours' into Dl+1 .. Dl+FL_HALO /
+// 1-FL_HALO .. 0 (every slab has at least FL_HALO planes).
 int fl_halo_exchange_on(fluid_handle* h, int n, float* const* fields, cudaStream_t stream)
 {
     if (h->nranks == 1) return 0;
     SlabComm* c = (SlabComm*)h->comm;
     if (!c || !c->comm) return fl_fail(h, FLUID_E_COMM, "halo exchange: no communicator attached to this slab handle (fluid_comm_init)");
-    const size_t cnt = 2 * (size_t)h->g.plane;
+    const size_t cnt = FL_HALO * (size_t)h->g.plane;
     const long long pl = h->g.plane;
     const int Dl = h->g.Dl;
     FL_NCCL(h, c, c->GroupStart());
@@ -76,10 +77,10 @@ int fl_halo_exchange_on(fluid_handle* h, int n, float* const* fields, cudaStream
         float* f = fields[i];
         if (h->rank > 0) {
             FL_NCCL(h, c, c->Send(f + 1 * pl, cnt, ncclFloat, h->rank - 1, c->comm, stream));
-            FL_NCCL(h, c, c->Recv(f - 1 * pl, cnt, ncclFloat, h->rank - 1, c->comm, stream));
+            FL_NCCL(h, c, c->Recv(f - (long long)(FL_HALO - 1) * pl, cnt, ncclFloat, h->rank - 1, c->comm, stream));
         }
         if (h->rank < h->nranks - 1) {
-            FL_NCCL(h, c, c->Send(f + (long long)(Dl - 1) * pl, cnt, ncclFloat, h->rank + 1, c->comm, stream));
+            FL_NCCL(h, c, c->Send(f + (long long)(Dl - FL_HALO + 1) * pl, cnt, ncclFloat, h->rank + 1, c->comm, stream));
             FL_NCCL(h, c, c->Recv(f + (long long)(Dl + 1) * pl, cnt, ncclFloat, h->rank + 1, c->comm, stream));
         }
     }
@@ -108,8 +109,8 @@ static inline float* fl_peer_ptr(fluid_handle* h, int r, const float* local)
     SlabComm* c = (SlabComm*)h->comm;
     if (!c) return nullptr;
     for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
-        if (h->alloc_base[i] == local - h->g.plane)
-            return c->peer_alloc[r][i] ? c->peer_alloc[r][i] + h->g.plane : nullptr;
+        if (h->alloc_base[i] == local - FL_ZPAD * h->g.plane)
+            return c->peer_alloc[r][i] ? c->peer_alloc[r][i] + FL_ZPAD * h->g.plane : nullptr;
     return nullptr;
 }
 

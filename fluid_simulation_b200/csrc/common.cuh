@@ -7,14 +7,18 @@
 // multiple of 16 B (the TMA requirement).  The reference layout (x + y*(W+2) + z*(W+2)*(H+2),
 // simulation.h:9) only exists in the pack/unpack kernels at the host boundary.
 // zl is the LOCAL plane index of a z-slab: global z = zlo + zl - 1 (zlo = 1, Dl = D on one GPU).
-// Every volume is allocated with planes zl = -1 .. Dl+2 (the field pointer addresses plane 0): a slab
-// keeps TWO halo planes per interior side, because one fused red-black sweep needs the colour-0 update
-// of the neighbour's boundary plane, which is recomputed locally from the second halo plane.
+// Every volume is allocated with planes zl = -FL_ZPAD .. Dl+1+FL_ZPAD (the field pointer addresses plane 0).
+// A slab keeps FL_HALO = 4 halo planes per interior side: one fused red-black sweep needs TWO (the colour-0
+// update of the neighbour's boundary plane is recomputed locally from the second halo plane), the pass
+// that fuses two sweeps needs four.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #define FL_XOFF 3
+#define FL_HALO 4    // halo planes a z-slab keeps per interior side: one temporally blocked pass (two red-black
+                     // sweeps, sweep_pair_kernel.cuh) reads its input four planes beyond the planes it owns
+#define FL_ZPAD 4    // planes allocated below local plane 0 and above plane Dl+1 (local planes -4 .. Dl+5)
 
 // per-cell flag byte, built once from obs (k_build_flags)
 #define FL_SOLID   0x01u   // obs == 1.0f                       (simulation.cpp:222, 301, 326, 375)
@@ -32,8 +36,8 @@ struct Grid {
     int pitch;            // floats per x-row
     int rows;             // H + 2
     long long plane;      // pitch * rows
-    long long cells;      // plane * (Dl + 4)   (allocated floats per field, planes -1 .. Dl+2)
-    int zl_lo, zl_hi;     // local planes that hold real data: 0 / Dl+1 at the tunnel ends, -1 / Dl+2 inside
+    long long cells;      // plane * (Dl + 2 + 2 * FL_ZPAD)   (allocated floats per field)
+    int zl_lo, zl_hi;     // local planes that hold real data: 0 / Dl+1 at the tunnel ends, 1-FL_HALO / Dl+FL_HALO inside
     int nxq;              // ceil(W / 4) x-quads per row
 };
 

@@ -21,9 +21,9 @@ static Grid make_grid(int w, int h, int d, int zlo, int dl, int rank, int nranks
     g.pitch = (w + 2 + FL_XOFF + 3) / 4 * 4;
     g.rows = h + 2;
     g.plane = (long long)g.pitch * g.rows;
-    g.cells = g.plane * (dl + 4);
-    g.zl_lo = rank == 0 ? 0 : -1;
-    g.zl_hi = rank == nranks - 1 ? dl + 1 : dl + 2;
+    g.cells = g.plane * (dl + 2 + 2 * FL_ZPAD);
+    g.zl_lo = rank == 0 ? 0 : 1 - FL_HALO;
+    g.zl_hi = rank == nranks - 1 ? dl + 1 : dl + FL_HALO;
     g.nxq = (w + 3) / 4;
     return g;
 }
@@ -35,23 +35,23 @@ static int alloc_all(fluid_handle* h)
     const size_t fbytes = (size_t)h->g.cells * sizeof(float);
     // one zeroed guard row in front of and behind every field keeps the float4 / scalar
     // neighbour loads of ghost-adjacent quads inside the allocation
-    // the handle's pointers address local plane 0; plane -1 precedes them (fl_base gives the allocation)
+    // the handle's pointers address local plane 0; FL_ZPAD planes precede them
     for (int i = 0; i < FLUID_NFIELDS; ++i) {
         FL_CUDA(h, cudaMalloc(&h->field[i], fbytes));
         FL_CUDA(h, cudaMemsetAsync(h->field[i], 0, fbytes, h->stream));   // simulation.cpp:38-43
         h->alloc_base[i] = h->field[i];
-        h->field[i] += h->g.plane;
+        h->field[i] += FL_ZPAD * h->g.plane;
     }
     for (int i = 0; i < 3; ++i) {
         FL_CUDA(h, cudaMalloc(&h->scratch[i], fbytes));
         FL_CUDA(h, cudaMemsetAsync(h->scratch[i], 0, fbytes, h->stream));
         h->alloc_base[FLUID_NFIELDS + i] = h->scratch[i];
-        h->scratch[i] += h->g.plane;
+        h->scratch[i] += FL_ZPAD * h->g.plane;
     }
     FL_CUDA(h, cudaMalloc(&h->cflags, (size_t)h->g.cells));
     FL_CUDA(h, cudaMemsetAsync(h->cflags, 0, (size_t)h->g.cells, h->stream));
-    h->cflags += h->g.plane;
-    FL_CUDA(h, cudaMalloc(&h->staging, ref_plane_floats(h->g) * (h->g.Dl + 4) * sizeof(float)));
+    h->cflags += FL_ZPAD * h->g.plane;
+    FL_CUDA(h, cudaMalloc(&h->staging, ref_plane_floats(h->g) * (h->g.Dl + 2 * FL_HALO) * sizeof(float)));
     h->n_partial = 148 * 8;
     FL_CUDA(h, cudaMalloc(&h->d_partial, (size_t)h->n_partial * FL_NSTAT * sizeof(double)));
     FL_CUDA(h, cudaMalloc(&h->d_out, FL_NSTAT * sizeof(double)));
@@ -64,7 +64,7 @@ static fluid_handle* create_impl(int w, int hgt, int d, int speed, float dt, flo
                                  int acc, unsigned flags, int rank, int nranks)
 {
     if (w < 1 || hgt < 1 || d < 1 || acc < 0 || nranks < 1 || rank < 0 || rank >= nranks || nranks > 8 ||
-        (nranks > 1 && d < 2 * nranks)) {
+        (nranks > 1 && d < FL_HALO * nranks)) {
         fl_fail(nullptr, FLUID_E_ARG, "fluid_create: bad arguments (w=%d h=%d d=%d acc=%d rank=%d/%d)",
                 w, hgt, d, acc, rank, nranks);
         return nullptr;
@@ -152,10 +152,10 @@ void fluid_destroy(fluid_handle* h)
     if (h->dump_stream) cudaStreamSynchronize(h->dump_stream);
     fl_tiled_release(h);
     fl_comm_release(h);
-    for (int i = 0; i < FLUID_NFIELDS; ++i) if (h->field[i]) cudaFree(h->field[i] - h->g.plane);
-    for (int i = 0; i < 4; ++i) if (h->scratch[i]) cudaFree(h->scratch[i] - h->g.plane);
+    for (int i = 0; i < FLUID_NFIELDS; ++i) if (h->field[i]) cudaFree(h->field[i] - FL_ZPAD * h->g.plane);
+    for (int i = 0; i < 4; ++i) if (h->scratch[i]) cudaFree(h->scratch[i] - FL_ZPAD * h->g.plane);
     for (int i = 0; i < 5; ++i) cudaFree(h->frame_staging[i]);
-    if (h->cflags) cudaFree(h->cflags - h->g.plane);
+    if (h->cflags) cudaFree(h->cflags - FL_ZPAD * h->g.plane);
     cudaFree(h->staging); cudaFree(h->d_partial); cudaFree(h->d_out);
     cudaFree(h->d_xyz); cudaFree(h->d_val); cudaFree(h->d_sync);
     for (auto& r : h->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }

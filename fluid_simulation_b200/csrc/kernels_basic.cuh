@@ -54,19 +54,21 @@ __global__ void __launch_bounds__(256) k_pack_rows(Grid g, int zl_first, int npl
 // Encodes exactly the obs tests the reference performs: `== 1.0f` for solid, `== 0.0f` plus the
 // 1..dim range test for "open" neighbours (simulation.cpp:222, 232-238, 307-312, 329-355).
 // obs has valid halo planes in slab mode, so the +-z tests see the neighbouring slab's mask.
-// obs / flags are the ALLOCATION bases (plane -1 first); index t runs over the whole allocation.
+// obs / flags are the ALLOCATION bases (plane -FL_ZPAD first); index t runs over the whole allocation.
 __global__ void k_build_flags(Grid g, const float* __restrict__ obs, unsigned char* __restrict__ flags)
 {
     long long n = g.cells;
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n;
          t += (long long)gridDim.x * blockDim.x) {
         long long r = t;
-        int zl = (int)(r / g.plane); r -= (long long)zl * g.plane; zl -= 1;
+        int zl = (int)(r / g.plane); r -= (long long)zl * g.plane; zl -= FL_ZPAD;
         int y = (int)(r / g.pitch);
         int x = (int)(r - (long long)y * g.pitch) - FL_XOFF;
         int gz = g.zlo + zl - 1;
         unsigned f = 0;
-        if (x >= 1 && x <= g.W && y >= 1 && y <= g.H && zl >= 1 && zl <= g.Dl) {
+        // owned planes and, on a z-slab, the halo planes the temporally blocked sweep zeroes cells on (their own
+        // z-neighbours are held too); everything outside the tunnel's interior stays 0
+        if (x >= 1 && x <= g.W && y >= 1 && y <= g.H && gz >= 1 && gz <= g.D && zl >= 2 - FL_HALO && zl <= g.Dl + FL_HALO - 1) {
             const float o = obs[t];
             const bool inxp = x + 1 <= g.W, inxm = x - 1 >= 1, inyp = y + 1 <= g.H, inym = y - 1 >= 1;
             const bool inzp = gz + 1 <= g.D, inzm = gz - 1 >= 1;
@@ -93,7 +95,7 @@ __global__ void k_build_flags(Grid g, const float* __restrict__ obs, unsigned ch
 __global__ void k_inflow_density(Grid g, float* __restrict__ dens, float amount)
 {
     int y = 1 + blockIdx.x * blockDim.x + threadIdx.x;
-    int zl = (int)blockIdx.y - 1;                // -1 .. Dl+2: a slab also keeps its two halo planes current
+    int zl = (int)blockIdx.y - (FL_HALO - 1);    // 1-FL_HALO .. Dl+FL_HALO: a slab also keeps its halo planes current
     int gz = g.zlo + zl - 1;
     if (y <= g.H && gz >= 1 && gz <= g.D) dens[fl_idx(g, 1, y, zl)] += amount;
 }
@@ -103,7 +105,7 @@ __global__ void k_inflow_velocity(Grid g, float* __restrict__ vx, float* __restr
                                   float* __restrict__ vz, float speed)
 {
     int y = 1 + blockIdx.x * blockDim.x + threadIdx.x;
-    int zl = (int)blockIdx.y - 1;
+    int zl = (int)blockIdx.y - (FL_HALO - 1);
     int gz = g.zlo + zl - 1;
     if (y <= g.H && gz >= 1 && gz <= g.D) {
         long long c = fl_idx(g, 1, y, zl);

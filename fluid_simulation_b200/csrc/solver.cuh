@@ -29,8 +29,8 @@ int fl_barrier(fluid_handle* h);                                         // comm
 static inline int fl_rebuild_flags(fluid_handle* h)
 {
     if (!h->flags_dirty) return 0;
-    k_build_flags<<<fl_grid_1d(h->g.cells), 256, 0, h->stream>>>(h->g, h->field[FLUID_OBS] - h->g.plane,
-                                                                 h->cflags - h->g.plane);
+    k_build_flags<<<fl_grid_1d(h->g.cells), 256, 0, h->stream>>>(h->g, h->field[FLUID_OBS] - FL_ZPAD * h->g.plane,
+                                                                 h->cflags - FL_ZPAD * h->g.plane);
     FL_CHECK_LAUNCH(h);
     h->flags_dirty = false;
     ++h->flags_version;
@@ -237,7 +237,7 @@ static inline int fl_advect(fluid_handle* h, int b, int fid, int pid)     // sim
 
 static inline int fl_inflow_density(fluid_handle* h)                      // simulation.cpp:65-67
 {
-    dim3 grid((h->g.H + 127) / 128, h->g.Dl + 4);
+    dim3 grid((h->g.H + 127) / 128, h->g.Dl + 2 * FL_HALO);
     k_inflow_density<<<grid, 128, 0, h->stream>>>(h->g, h->field[FLUID_DENS], 0.001f);
     FL_CHECK_LAUNCH(h);
     return 0;
@@ -245,7 +245,7 @@ static inline int fl_inflow_density(fluid_handle* h)                      // sim
 
 static inline int fl_inflow_velocity(fluid_handle* h)                     // simulation.cpp:103-105
 {
-    dim3 grid((h->g.H + 127) / 128, h->g.Dl + 4);
+    dim3 grid((h->g.H + 127) / 128, h->g.Dl + 2 * FL_HALO);
     k_inflow_velocity<<<grid, 128, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY],
                                                    h->field[FLUID_VZ], (float)h->speed);
     FL_CHECK_LAUNCH(h);
@@ -254,7 +254,7 @@ static inline int fl_inflow_velocity(fluid_handle* h)                     // sim
 
 static inline int fl_copy_field(fluid_handle* h, int dst, int src)
 {
-    FL_CUDA(h, cudaMemcpyAsync(h->field[dst] - h->g.plane, h->field[src] - h->g.plane, (size_t)h->g.cells * sizeof(float),
+    FL_CUDA(h, cudaMemcpyAsync(h->field[dst] - FL_ZPAD * h->g.plane, h->field[src] - FL_ZPAD * h->g.plane, (size_t)h->g.cells * sizeof(float),
                                cudaMemcpyDeviceToDevice, h->stream));
     return 0;
 }

@@ -8,18 +8,20 @@
 
 // One bit per cell: "setBounds zeroes this cell" for scalars ([0]: solid) and for velocity components
 // ([1]: solid or touching a solid), simulation.cpp:219-245.  Layout: one 16-bit word per (plane, row pair,
-// lane): bits 0-7 = cells 1 + 8*lane .. + 7 of row 2*pair, bits 8-15 = the same cells of row 2*pair + 1.
+// lane), local planes 1-FL_HALO .. Dl+FL_HALO: bits 0-7 = cells 1 + 8*lane .. + 7 of row 2*pair, bits 8-15 = the
+// same cells of row 2*pair + 1.
 // 2 x 2 MB at 256^3: the sweeps read them from L2 instead of 1 byte per cell from HBM.
 __global__ void __launch_bounds__(256) k_build_zbits(Grid g, const unsigned char* __restrict__ flags,
                                                      unsigned short* __restrict__ z0, unsigned short* __restrict__ z1, int pairs)
 {
-    const long long n = (long long)(g.Dl + 2) * pairs * 32;
+    const long long n = (long long)(g.Dl + 2 * FL_HALO) * pairs * 32;
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
         const int lane = (int)(t & 31);
         const long long r = t >> 5;
-        const int pr = (int)(r % pairs), zl = (int)(r / pairs);
+        const int pr = (int)(r % pairs), zl = (int)(r / pairs) - (FL_HALO - 1);
         unsigned s0 = 0u, s1 = 0u;
-        if (zl >= 1 && zl <= g.Dl)
+        // the flag volume is non-zero exactly where a cell of the tunnel's interior is held with its z-neighbours
+        if (zl >= 2 - FL_HALO && zl <= g.Dl + FL_HALO - 1)
             for (int k = 0; k < 2; ++k) {
                 const int y = 2 * pr + k;
                 if (y < 1 || y > g.H) continue;
@@ -50,11 +52,15 @@ void sw_pair_release(StreamState* s)
     s->pair = nullptr;
 }
 
+// FLUID_PAIR=1 switches the temporally blocked kernel on.  It is OFF by default: measured on B200 at 256^3 it
+// halves the HBM traffic per sweep (140 instead of 242 MB, ncu) but is bound by instruction issue at 8 warps
+// per SM and ends up level with k_sweep_stream (47.7 vs 46.5 us per single-field sweep, 44.6 vs 42.9 us in the
+// step mix; profiles/r02_pair_*).  Read per solve so that tests can A/B inside one process.
 inline bool fl_pair_eligible(fluid_handle* h)
 {
-    const bool off = getenv("FLUID_NO_PAIR") != nullptr;             // read per solve: tests A/B it inside one process
+    const char* on = getenv("FLUID_PAIR");
     const Grid& g = h->g;
-    if (off || h->nranks != 1 || (h->flags & FLUID_SOLVER_MASK) != FLUID_SOLVER_RB) return false;
+    if (!on || atoi(on) == 0 || h->nranks != 1 || (h->flags & FLUID_SOLVER_MASK) != FLUID_SOLVER_RB) return false;
     return g.W > 128 && g.W <= 256 && (g.W & 7) == 0 && (g.H & 1) == 0 && g.cells < (1ll << 32);
 }
 
@@ -78,12 +84,12 @@ inline int sw_pair_run(fluid_handle* h, int nb, const int* b, const int* fid, co
     PairState* ps = (PairState*)s->pair;
     if (!ps->zbits[0]) {
         ps->pairs = (g.rows + 1) / 2;
-        const size_t n = (size_t)(g.Dl + 2) * ps->pairs * 32 * sizeof(unsigned short);
+        const size_t n = (size_t)(g.Dl + 2 * FL_HALO) * ps->pairs * 32 * sizeof(unsigned short);
         FL_CUDA(h, cudaMalloc(&ps->zbits[0], n));
         FL_CUDA(h, cudaMalloc(&ps->zbits[1], n));
     }
     if (ps->flags_version != h->flags_version) {
-        const long long n = (long long)(g.Dl + 2) * ps->pairs * 32;
+        const long long n = (long long)(g.Dl + 2 * FL_HALO) * ps->pairs * 32;
         k_build_zbits<<<fl_grid_1d(n), 256, 0, h->stream>>>(g, h->cflags, ps->zbits[0], ps->zbits[1], ps->pairs);
         FL_CHECK_LAUNCH(h);
         ps->flags_version = h->flags_version;
@@ -100,7 +106,7 @@ inline int sw_pair_run(fluid_handle* h, int nb, const int* b, const int* fid, co
         const size_t fb = (size_t)g.cells * sizeof(float);
         FL_CUDA(h, cudaMalloc(&h->scratch[3], fb));
         FL_CUDA(h, cudaMemsetAsync(h->scratch[3], 0, fb, h->stream));
-        h->scratch[3] += g.plane;
+        h->scratch[3] += FL_ZPAD * g.plane;
     }
     for (int i = 0; i < nb; ++i) {
         cur[i] = h->field[fid[i]]; alt[i] = h->scratch[i];
@@ -150,9 +156,10 @@ int fl_pair_solve(fluid_handle* h, int nb, const int* b, const int* fid, const i
     *done = 0;
     const int npairs = h->acc / 2;
     if (npairs <= 0 || !fl_pair_eligible(h)) return 0;
-    // FLUID_PAIR_UNROLL=2: the two-step loop body with a ring rotation (a third of the code) instead of six
+    // FLUID_PAIR_UNROLL=6: six unrolled steps (no register moves, three times the code; measured slower:
+    // instruction fetch) instead of the two-step loop body with a ring rotation
     const char* u = getenv("FLUID_PAIR_UNROLL");
-    if (u && atoi(u) == 2) { if (int e = sw_pair_run<8, 2>(h, nb, b, fid, pid, a, c, x_from_rhs, npairs)) return e; }
+    if (!u || atoi(u) == 2) { if (int e = sw_pair_run<8, 2>(h, nb, b, fid, pid, a, c, x_from_rhs, npairs)) return e; }
     else                   { if (int e = sw_pair_run<8, 6>(h, nb, b, fid, pid, a, c, x_from_rhs, npairs)) return e; }
     *done = 2 * npairs;
     return 0;

@@ -10,7 +10,7 @@
 // and one pipeline step runs four half-sweeps ("stages"), each one plane behind the previous:
 //   stage 0: colour 0 of sweep 1 on plane p      stage 1: colour 1 of sweep 1 on plane p-1 (+ setBounds)
 //   stage 2: colour 0 of sweep 2 on plane p-2    stage 3: colour 1 of sweep 2 on plane p-3, store
-// Colour c of a cell = (x + y + z) & 1, colour 0 first -- the ordering-matched CPU loop of the oracle.
+// Colour c of a cell = (x + y + z) & 1, colour 0 first -- the order of the CPU checker's red-black loop.
 // A cell's update does not read its own value (simulation.cpp:263-269), and in one step all four stages
 // act on the same in-register positions (row A: positions i = E mod 2, row B: the others; E alternates
 // with p), so the ring just shifts by one plane per step.
@@ -70,7 +70,7 @@ struct alignas(64) PairArgs {
     CUtensorMap rmap[4];                 // its right-hand side (box SW_RBOXW x TR x 1)
     float* dst[4];
     int b[4];
-    const unsigned short* zbits[2];      // [0]: solid, [1]: solid | no-slip; one bit per cell, see k_build_zbits
+    const unsigned short* zbits[2];      // [0]: solid, [1]: solid | no-slip; one bit per cell, local planes 1-FL_HALO .. Dl+FL_HALO (k_build_zbits)
     const SwSeg* segs;                   // CTA k works through segs[seg_first[k] .. seg_first[k+1])
     const int* seg_first;
     Grid g;
@@ -136,8 +136,7 @@ struct SpThread {
     int offA, roffA, sA;                 // row A: offsets into an x slot, a rhs slot, a published colour plane
     bool intA, intB;                     // row is an interior row of the grid (takes part in the stages)
     bool ghostA, ghostB;                 // row is the y = 0 / y = H+1 ghost row (its pair partner is y = 1 / y = H)
-    bool ownA, ownB;                     // row is stored by this CTA
-    int smaxA, smaxB;                    // last stage that is still needed on the row (halo rows: fewer)
+    bool ownA, ownB;                     // this thread's octet of the row is stored by this CTA
     bool lane_in;
     unsigned eA, eB;                     // x / y edge bits of the store epilogue
     // rings indexed like the plane ring (SP_SLOT): only the entries of planes p .. p-3 are live
@@ -160,24 +159,55 @@ __device__ __forceinline__ float4 sp_lds_half(const float* p, unsigned& sink)
     return sp_pick<PE>(v0, v1);
 }
 
+// ---- the rare part of the store epilogue, out of line: face ghosts of one finished octet row ---------
+// (simulation.cpp:187-215: ghosts take the PRE-zero value; x = 0 negates for b == 1, y faces for b == 2,
+// z faces for b == 3, x = W+1 is a plain copy).  Called by the few threads that sit on a face.
+__device__ __noinline__ void sp_store_ghosts(const Grid g, float* __restrict__ out, unsigned c, float4 r0, float4 r1,
+                                             int b, unsigned edge)
+{
+    if (edge & SW_XLO) out[c - 1] = (b == 1) ? -r0.x : r0.x;
+    if (edge & SW_XHI) out[c + 8] = r1.w;
+    if (edge & (SW_YLO | SW_YHI)) {
+        const float4 g0 = (b == 2) ? sp_neg(r0) : r0, g1 = (b == 2) ? sp_neg(r1) : r1;
+        if (edge & SW_YLO) { st4(out + c - g.pitch, g0); st4(out + c - g.pitch + 4, g1); }
+        if (edge & SW_YHI) { st4(out + c + g.pitch, g0); st4(out + c + g.pitch + 4, g1); }
+    }
+    if (edge & (SW_ZLO | SW_ZHI)) {
+        const float4 g0 = (b == 3) ? sp_neg(r0) : r0, g1 = (b == 3) ? sp_neg(r1) : r1;
+        if (edge & SW_ZLO) { st4(out + c - g.plane, g0); st4(out + c - g.plane + 4, g1); }
+        if (edge & SW_ZHI) { st4(out + c + g.plane, g0); st4(out + c + g.plane + 4, g1); }
+    }
+}
+
+// one finished octet row: zero solids / no-slip cells (bits: bit i = position i), store, ghosts if on a face
+__device__ __forceinline__ void sp_store_row(const Grid& g, float* __restrict__ out, unsigned c, const float4& r0,
+                                             const float4& r1, unsigned bits, int b, unsigned edge)
+{
+    st4(out + c,     make_float4((bits & 1u) ? 0.0f : r0.x, (bits & 2u) ? 0.0f : r0.y, (bits & 4u) ? 0.0f : r0.z,
+                                 (bits & 8u) ? 0.0f : r0.w));
+    st4(out + c + 4, make_float4((bits & 16u) ? 0.0f : r1.x, (bits & 32u) ? 0.0f : r1.y, (bits & 64u) ? 0.0f : r1.z,
+                                 (bits & 128u) ? 0.0f : r1.w));
+    if (edge) sp_store_ghosts(g, out, c, r0, r1, b, edge);
+}
+
 // ---- one half-sweep on one plane ------------------------------------------------------------------
-// S = stage, E = parity of the step, UP = planes streamed upwards in z.  c = the plane the stage acts on,
-// ahead / behind = its stream neighbours (z+1 / z-1 when UP).  ynbr: S == 0: the x slot of the plane
-// (natural layout), else the colour plane published by the previous stage one step ago.  spub: where this
-// stage publishes its colour (S < 3).  rslot: the plane's right-hand side.  k = ring position of the plane
-// (xg / fz index) = S.
+// S = stage, U = unroll position (parity E = U & 1), UP = planes streamed upwards in z.  c = the plane the
+// stage acts on, ahead / behind = its stream neighbours (z+1 / z-1 when UP).  ynbr: S == 0: the x slot of
+// the plane (natural layout), else the colour plane published by the previous stage one step ago.  spub:
+// where this stage publishes its colour (S < 3).  rA / rB: right-hand side of the active cells.
+// Both rows are relaxed unconditionally in one basic block (eight independent cells in flight): a row that
+// lies outside the grid, or is a halo row the stage is no longer needed on, computes values nobody uses;
+// only the y ghost rows have to keep theirs (intA / intB guard the write-back).
 template <int S, int U, bool UP>
 __device__ __forceinline__ void sp_stage(SpThread& t, const PairArgs& A, SpPlane& c, SpPlane& ahead, SpPlane& behind,
                                          const float* __restrict__ ynbr, float* __restrict__ spub,
-                                         const float4& rA, const float4& rB, int b, int zg, bool in_window,
+                                         const float4& rA, const float4& rB, int b, int zg,
                                          float* __restrict__ out, unsigned oA, bool store_plane)
 {
     constexpr int E = U & 1;                               // segments start on an even step (see sp_segment)
     constexpr int PA = E, PB = 1 - E;                      // active positions of row A / row B
     constexpr int K = SP_SLOT(S + 1, U), K1 = SP_SLOT(2, U), K3 = SP_SLOT(4, U);   // ring slots of this plane, of planes p-1 / p-3
     const float a = A.a, cr = A.c_recip;
-    const bool doA = in_window && t.intA && S <= t.smaxA, doB = in_window && t.intB && S <= t.smaxB;
-    if (!doA && !doB) return;                              // warp-uniform
     SpPlane& zpP = UP ? ahead : behind;
     SpPlane& zmP = UP ? behind : ahead;
     // x neighbours across lanes: row A needs L when PA == 0, else R; row B the other one
@@ -189,42 +219,32 @@ __device__ __forceinline__ void sp_stage(SpThread& t, const PairArgs& A, SpPlane
         RA = __shfl_down_sync(0xffffffffu, c.a0.x, 1); RA = t.hi_lane ? t.xgA[K] : RA;
         LB = __shfl_up_sync(0xffffffffu, c.b1.w, 1);   LB = t.lo_lane ? t.xgB[K] : LB;
     }
-    float4 nA = make_float4(0.0f, 0.0f, 0.0f, 0.0f), nB = nA;
-    if (doA) {
-        float4 ym;
-        if (S == 0) ym = sp_lds_half<PA>(ynbr + t.offA - SW_BOXW, t.sink);
-        else        ym = sw_lds4(ynbr + t.sA - SP_SROW);
-        nA = sp_relax<PA>(c.a0, c.a1, LA, RA, sp_pick<PA>(c.b0, c.b1), ym, sp_pick<PA>(zpP.a0, zpP.a1),
-                          sp_pick<PA>(zmP.a0, zmP.a1), rA, a, cr);
-    }
-    if (doB) {
-        float4 yp;
-        if (S == 0) yp = sp_lds_half<PB>(ynbr + t.offA + 2 * SW_BOXW, t.sink);
-        else        yp = sw_lds4(ynbr + t.sA + 2 * SP_SROW);
-        nB = sp_relax<PB>(c.b0, c.b1, LB, RB, yp, sp_pick<PB>(c.a0, c.a1), sp_pick<PB>(zpP.b0, zpP.b1),
-                          sp_pick<PB>(zmP.b0, zmP.b1), rB, a, cr);
-    }
-    // both rows were relaxed from the values before this stage; now they take their new values
+    float4 ym, yp;
+    if (S == 0) { ym = sp_lds_half<PA>(ynbr + t.offA - SW_BOXW, t.sink); yp = sp_lds_half<PB>(ynbr + t.offA + 2 * SW_BOXW, t.sink); }
+    else        { ym = sw_lds4(ynbr + t.sA - SP_SROW);                   yp = sw_lds4(ynbr + t.sA + 2 * SP_SROW); }
+    float4 nA = sp_relax<PA>(c.a0, c.a1, LA, RA, sp_pick<PA>(c.b0, c.b1), ym, sp_pick<PA>(zpP.a0, zpP.a1),
+                             sp_pick<PA>(zmP.a0, zmP.a1), rA, a, cr);
+    float4 nB = sp_relax<PB>(c.b0, c.b1, LB, RB, yp, sp_pick<PB>(c.a0, c.a1), sp_pick<PB>(zpP.b0, zpP.b1),
+                             sp_pick<PB>(zmP.b0, zmP.b1), rB, a, cr);
     if (S < 2) {
         // ---- sweep 1: what setBounds will make of the ghosts next to these cells (simulation.cpp:187-215),
         // from the PRE-zero values; each ghost is read only by the cell it mirrors ----------------------
-        if (doA) {
-            if (PA == 0) t.xgA[K] = t.lo_lane ? ((b == 1) ? -nA.x : nA.x) : t.xgA[K];    // x = 0      :189
-            else         t.xgA[K] = t.hi_lane ? nA.w : t.xgA[K];                         // x = W + 1  :191
+        if (PA == 0) {
+            t.xgA[K] = t.lo_lane ? ((b == 1) ? -nA.x : nA.x) : t.xgA[K];                 // x = 0      :189
+            t.xgB[K] = t.hi_lane ? nB.w : t.xgB[K];                                      // x = W + 1  :191
+        } else {
+            t.xgA[K] = t.hi_lane ? nA.w : t.xgA[K];
+            t.xgB[K] = t.lo_lane ? ((b == 1) ? -nB.x : nB.x) : t.xgB[K];
         }
-        if (doB) {
-            if (PB == 0) t.xgB[K] = t.lo_lane ? ((b == 1) ? -nB.x : nB.x) : t.xgB[K];
-            else         t.xgB[K] = t.hi_lane ? nB.w : t.xgB[K];
-        }
-        if (t.ghostA && doB) sp_put<PB>(c.a0, c.a1, b == 2 ? sp_neg(nB) : nB);           // y = 0      :198
-        if (t.ghostB && doA) sp_put<PA>(c.b0, c.b1, b == 2 ? sp_neg(nA) : nA);           // y = H + 1  :200
+        if (t.ghostA) sp_put<PB>(c.a0, c.a1, b == 2 ? sp_neg(nB) : nB);                  // y = 0      :198
+        if (t.ghostB) sp_put<PA>(c.b0, c.b1, b == 2 ? sp_neg(nA) : nA);                  // y = H + 1  :200
         if (zg == 1) {                                                                   // z = 0      :208
-            if (doA) sp_put<PA>(zmP.a0, zmP.a1, b == 3 ? sp_neg(nA) : nA);
-            if (doB) sp_put<PB>(zmP.b0, zmP.b1, b == 3 ? sp_neg(nB) : nB);
+            sp_put<PA>(zmP.a0, zmP.a1, b == 3 ? sp_neg(nA) : nA);
+            sp_put<PB>(zmP.b0, zmP.b1, b == 3 ? sp_neg(nB) : nB);
         }
         if (zg == A.g.D) {                                                               // z = D + 1  :212
-            if (doA) sp_put<PA>(zpP.a0, zpP.a1, b == 3 ? sp_neg(nA) : nA);
-            if (doB) sp_put<PB>(zpP.b0, zpP.b1, b == 3 ? sp_neg(nB) : nB);
+            sp_put<PA>(zpP.a0, zpP.a1, b == 3 ? sp_neg(nA) : nA);
+            sp_put<PB>(zpP.b0, zpP.b1, b == 3 ? sp_neg(nB) : nB);
         }
     }
     if (S == 1) {
@@ -233,30 +253,17 @@ __device__ __forceinline__ void sp_stage(SpThread& t, const PairArgs& A, SpPlane
         nA = sp_zero<PA>(nA, t.fz[K1]);
         nB = sp_zero<PB>(nB, t.fz[K1] >> 8);
     }
-    if (doA) sp_put<PA>(c.a0, c.a1, nA);
-    if (doB) sp_put<PB>(c.b0, c.b1, nB);
+    if (t.intA) sp_put<PA>(c.a0, c.a1, nA);
+    if (t.intB) sp_put<PB>(c.b0, c.b1, nB);
     if (S < 3) {
-        if (doA) sw_sts4(spub + t.sA, nA);
-        if (doB) sw_sts4(spub + t.sA + SP_SROW, nB);
+        sw_sts4(spub + t.sA, nA);
+        sw_sts4(spub + t.sA + SP_SROW, nB);
     } else if (store_plane) {
-        // ---- store with the setBounds epilogue of sweep 2 (sw_store: ghosts take the pre-zero value) ----
+        // ---- store with the setBounds epilogue of sweep 2 ----
         const Grid& g = A.g;
         const unsigned zbits = (zg == 1 ? SW_ZLO : 0u) | (zg == g.D ? SW_ZHI : 0u);
-        const unsigned zmask4 = 0x01010101u;               // the bits below are already class-selected
-        if (t.ownA && t.lane_in) {
-            const unsigned f = t.fz[K3];
-            const unsigned lo = (f & 1u) | ((f & 2u) << 7) | ((f & 4u) << 14) | ((f & 8u) << 21);
-            const unsigned hi = ((f >> 4) & 1u) | ((f & 0x20u) << 3) | ((f & 0x40u) << 10) | ((f & 0x80u) << 17);
-            sw_store(g, out, oA, c.a0, lo, b, zmask4, (t.eA & ~SW_XHI) | zbits);
-            sw_store(g, out, oA + 4, c.a1, hi, b, zmask4, (t.eA & ~SW_XLO) | zbits);
-        }
-        if (t.ownB && t.lane_in) {
-            const unsigned f = t.fz[K3] >> 8;
-            const unsigned lo = (f & 1u) | ((f & 2u) << 7) | ((f & 4u) << 14) | ((f & 8u) << 21);
-            const unsigned hi = ((f >> 4) & 1u) | ((f & 0x20u) << 3) | ((f & 0x40u) << 10) | ((f & 0x80u) << 17);
-            sw_store(g, out, oA + g.pitch, c.b0, lo, b, zmask4, (t.eB & ~SW_XHI) | zbits);
-            sw_store(g, out, oA + g.pitch + 4, c.b1, hi, b, zmask4, (t.eB & ~SW_XLO) | zbits);
-        }
+        if (t.ownA) sp_store_row(g, out, oA, c.a0, c.a1, t.fz[K3] & 0xffu, b, t.eA | zbits);
+        if (t.ownB) sp_store_row(g, out, oA + (unsigned)g.pitch, c.b0, c.b1, (t.fz[K3] >> 8) & 0xffu, b, t.eB | zbits);
     }
 }
 
@@ -282,18 +289,20 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
     float* __restrict__ out = A.dst[batch];
     const unsigned short* __restrict__ zbv = A.zbits[b == 0 ? 0 : 1];
 
-    // windows: stage s runs on planes za-(3-s) .. zb+(3-s), clipped to the interior 1 .. D
-    const int wlo0 = max(za - 3, 1), whi0 = min(zb + 3, g.D);
-    const int wlo1 = max(za - 2, 1), whi1 = min(zb + 2, g.D);
-    const int wlo2 = max(za - 1, 1), whi2 = min(zb + 1, g.D);
+    // windows: stage s runs on planes za-(3-s) .. zb+(3-s), clipped to the interior of the TUNNEL (global
+    // z = 1 .. D are the local planes zmin .. zmax; a z-slab recomputes up to three planes of each neighbour)
+    const int zmin = 2 - g.zlo, zmax = g.D - g.zlo + 1;
+    const int wlo0 = max(za - 3, zmin), whi0 = min(zb + 3, zmax);
+    const int wlo1 = max(za - 2, zmin), whi1 = min(zb + 2, zmax);
+    const int wlo2 = max(za - 1, zmin), whi2 = min(zb + 1, zmax);
     // first stage-0 plane; the unrolled body fixes the parity of a step by its position, so a segment whose
     // first plane has the odd parity starts one (idle) step earlier: every window excludes that plane
     const int ps0 = UP ? wlo0 : whi0;
     const int ps = ((g.zlo + ps0) & 1) ? ps0 - DIR : ps0;
     const int pe = UP ? zb + 3 : za - 3;                         // plane index of the last step (stage 3 on zb / za)
     const int nsteps = (pe - ps) * DIR + 1;
-    const int first = ps - DIR;                                  // first plane loaded (-1 .. D+2: inside the allocation)
-    const int lastp = UP ? min(zb + 4, g.D + 1) : max(za - 4, 0);
+    const int first = ps - DIR;                                  // first plane loaded (-FL_ZPAD .. Dl+1+FL_ZPAD: inside the allocation)
+    const int lastp = UP ? min(zb + 4, zmax + 1) : max(za - 4, zmin - 1);
     const int nplanes = (lastp - first) * DIR + 1;
 
     auto issue = [&](int p) {                                    // plane p -> next ring slots
@@ -304,9 +313,9 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
             float* rs = rring + R.rs_iss * RSLOTF;
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-                // the tensor maps start at the allocation's plane -1, hence p + 1
-                sw_tma_load_3d(xs + i * BOXF, &A.map[batch], 128 * i, y0 - 4, p + 1, bar);
-                sw_tma_load_3d(rs + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 3, p + 1, bar);
+                // the tensor maps start at the allocation's first plane, -FL_ZPAD
+                sw_tma_load_3d(xs + i * BOXF, &A.map[batch], 128 * i, y0 - 4, p + FL_ZPAD, bar);
+                sw_tma_load_3d(rs + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 3, p + FL_ZPAD, bar);
             }
         }
         if (++R.xs_iss == SP_NX) R.xs_iss = 0;
@@ -320,9 +329,8 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
     const int x0 = 1 + 8 * t.lane;
     t.intA = yA >= 1 && yA <= g.H; t.intB = yB >= 1 && yB <= g.H;
     t.ghostA = yA == 0; t.ghostB = yB == g.H + 1;
-    t.ownA = t.intA && w >= 2 && w <= NP - 2;
-    t.ownB = t.intB && w >= 1 && w <= NP - 3;
-    t.smaxA = min(2 * w, GE::TR - 1 - 2 * w); t.smaxB = min(2 * w + 1, GE::TR - 2 - 2 * w);
+    t.ownA = t.intA && w >= 2 && w <= NP - 2 && t.lane_in;
+    t.ownB = t.intB && w >= 1 && w <= NP - 3 && t.lane_in;
     t.eA = (yA == 1 ? SW_YLO : 0u) | (yA == g.H ? SW_YHI : 0u) | (x0 == 1 ? SW_XLO : 0u) | (x0 + 7 == g.W ? SW_XHI : 0u);
     t.eB = (yB == 1 ? SW_YLO : 0u) | (yB == g.H ? SW_YHI : 0u) | (x0 == 1 ? SW_XLO : 0u) | (x0 + 7 == g.W ? SW_XHI : 0u);
     // element offset of row A's octet in plane 0 (32-bit: the padded volume has < 2^32 cells); rows that are
@@ -331,6 +339,7 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
     const unsigned plane = (unsigned)g.plane;
     const unsigned zb_row = (unsigned)((yA >> 1) * 32 + t.lane);  // yA is even; pairs (2k, 2k+1)
     const bool zb_ok = yA >= 0 && yA <= g.H;
+    const int zlo_bits = max(zmin, 1 - FL_HALO), zhi_bits = min(zmax, g.Dl + FL_HALO);   // planes the zero-bit volume covers
 
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     SpPlane P[6];
@@ -374,7 +383,7 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
         /* x ghosts beside plane p as the last setBounds left them, and the plane's zero bits */               \
         t.xgA[SP_SLOT(1, U)] = edge_lane ? xs_p[xg_off] : 0.0f;                                                 \
         t.xgB[SP_SLOT(1, U)] = edge_lane ? xs_p[xg_off + SW_BOXW] : 0.0f;                                       \
-        t.fz[SP_SLOT(1, U)] = (zb_ok && p >= 1 && p <= g.D) ? (unsigned)zbv[(unsigned)p * (unsigned)(A.zb_pairs * 32) + zb_row] : 0u; \
+        t.fz[SP_SLOT(1, U)] = (zb_ok && p >= zlo_bits && p <= zhi_bits) ? (unsigned)zbv[(unsigned)(p + FL_HALO - 1) * (unsigned)(A.zb_pairs * 32) + zb_row] : 0u; \
         const int zg = g.zlo + p - 1;                                                                           \
         float* const S0w = sbuf + (0 + EE) * SBUFF;     const float* const S0r = sbuf + (0 + 1 - EE) * SBUFF;   \
         float* const S1w = sbuf + (2 + EE) * SBUFF;     const float* const S1r = sbuf + (2 + 1 - EE) * SBUFF;   \
@@ -383,19 +392,19 @@ __device__ __forceinline__ void sp_segment(const PairArgs& A, const SwSeg sg, Sp
         {                                                                                                       \
             const float* rp = rring + rs0 * RSLOTF + t.roffA;                                                   \
             const float4 u0 = sw_lds4(rp), u1 = sw_lds4(rp + 4), u2 = sw_lds4(rp + SW_RBOXW), u3 = sw_lds4(rp + SW_RBOXW + 4); \
-            sp_stage<0, U, UP>(t, A, C0, N, C1, xs_p, S0w, sp_pick<EE>(u0, u1), sp_pick<1 - EE>(u2, u3), b, zg, \
-                               p >= wlo0 && p <= whi0, out, 0u, false);                                         \
-            sp_stage<1, U, UP>(t, A, C1, C0, C2, S0r, S1w, t.h1A, t.h1B, b, zg - DIR,                           \
-                               q1 >= wlo1 && q1 <= whi1, out, 0u, false);                                       \
+            if (p >= wlo0 && p <= whi0)                                                                         \
+                sp_stage<0, U, UP>(t, A, C0, N, C1, xs_p, S0w, sp_pick<EE>(u0, u1), sp_pick<1 - EE>(u2, u3), b, zg, out, 0u, false); \
+            if (q1 >= wlo1 && q1 <= whi1)                                                                       \
+                sp_stage<1, U, UP>(t, A, C1, C0, C2, S0r, S1w, t.h1A, t.h1B, b, zg - DIR, out, 0u, false);      \
             t.h1A = sp_pick<1 - EE>(u0, u1); t.h1B = sp_pick<EE>(u2, u3);                                       \
         }                                                                                                       \
         {                                                                                                       \
             const float* rp = rring + rs2 * RSLOTF + t.roffA;                                                   \
             const float4 u0 = sw_lds4(rp), u1 = sw_lds4(rp + 4), u2 = sw_lds4(rp + SW_RBOXW), u3 = sw_lds4(rp + SW_RBOXW + 4); \
-            sp_stage<2, U, UP>(t, A, C2, C1, C3, S1r, S2w, sp_pick<EE>(u0, u1), sp_pick<1 - EE>(u2, u3), b, zg - 2 * DIR, \
-                               q2 >= wlo2 && q2 <= whi2, out, 0u, false);                                       \
-            sp_stage<3, U, UP>(t, A, C3, C2, C4, S2r, nullptr, t.h3A, t.h3B, b, zg - 3 * DIR,                   \
-                               q3 >= za && q3 <= zb, out, oA0 + (unsigned)q3 * plane, true);                    \
+            if (q2 >= wlo2 && q2 <= whi2)                                                                       \
+                sp_stage<2, U, UP>(t, A, C2, C1, C3, S1r, S2w, sp_pick<EE>(u0, u1), sp_pick<1 - EE>(u2, u3), b, zg - 2 * DIR, out, 0u, false); \
+            if (q3 >= za && q3 <= zb)                                                                           \
+                sp_stage<3, U, UP>(t, A, C3, C2, C4, S2r, nullptr, t.h3A, t.h3B, b, zg - 3 * DIR, out, oA0 + (unsigned)q3 * plane, true); \
             t.h3A = sp_pick<1 - EE>(u0, u1); t.h3B = sp_pick<EE>(u2, u3);                                       \
         }                                                                                                       \
         xs_p = xs_n; rs2 = rs1; rs1 = rs0; rs0 = rs_n; p += DIR; ++jc;                                          \

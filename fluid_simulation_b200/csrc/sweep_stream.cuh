@@ -402,9 +402,9 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
             float* slot = uring + s_iss * SLOTF;
 #pragma unroll
             for (int i = 0; i < TXW; ++i) {
-                // the tensor maps start at the allocation's plane -1, hence p + 1
-                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p + 1, bar);
-                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p + 1, bar);
+                // the tensor maps start at the allocation's first plane, -FL_ZPAD
+                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p + FL_ZPAD, bar);
+                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p + FL_ZPAD, bar);
             }
         }
         if (++s_iss == NSLOT) s_iss = 0;
@@ -609,11 +609,11 @@ inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows
     if (it == s->maps.end()) {
         const Grid& g = h->g;
         CUtensorMap m;
-        cuuint64_t dims[3] = { (cuuint64_t)g.pitch, (cuuint64_t)g.rows, (cuuint64_t)(g.Dl + 4) };   // planes -1 .. Dl+2
+        cuuint64_t dims[3] = { (cuuint64_t)g.pitch, (cuuint64_t)g.rows, (cuuint64_t)(g.Dl + 2 + 2 * FL_ZPAD) };   // planes -FL_ZPAD .. Dl+1+FL_ZPAD
         cuuint64_t strides[2] = { (cuuint64_t)g.pitch * 4, (cuuint64_t)g.plane * 4 };
         cuuint32_t box[3] = { (cuuint32_t)box_w, (cuuint32_t)box_rows, 1 };
         cuuint32_t estr[3] = { 1, 1, 1 };
-        CUresult r = s->encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)(buf - g.plane), dims, strides, box, estr,
+        CUresult r = s->encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)(buf - FL_ZPAD * g.plane), dims, strides, box, estr,
                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return fl_fail(h, FLUID_E_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
@@ -820,7 +820,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         const size_t fb = (size_t)g.cells * sizeof(float);
         FL_CUDA(h, cudaMalloc(&h->scratch[3], fb));
         FL_CUDA(h, cudaMemsetAsync(h->scratch[3], 0, fb, h->stream));
-        h->scratch[3] += g.plane;
+        h->scratch[3] += FL_ZPAD * g.plane;
     }
     for (int i = 0; i < nb; ++i) {
         cur[i] = h->field[fid[i]]; alt[i] = h->scratch[i];

@@ -20,6 +20,9 @@
 #include <cuda_runtime.h>                 // float4, make_float4, the (ignored) function qualifiers
 using std::max;
 using std::min;
+#ifndef __noinline__
+#define __noinline__ __attribute__((noinline))
+#endif
 static thread_local uint3 threadIdx, blockIdx;           // only named by helpers the emulation never calls
 static thread_local dim3 blockDim, gridDim;
 
@@ -95,7 +98,7 @@ static Grid make_grid(int w, int h, int d)
     g.pitch = (w + 2 + FL_XOFF + 3) / 4 * 4;
     g.rows = h + 2;
     g.plane = (long long)g.pitch * g.rows;
-    g.cells = g.plane * (d + 4);
+    g.cells = g.plane * (d + 2 + 2 * FL_ZPAD);
     g.zl_lo = 0; g.zl_hi = d + 1;
     g.nxq = (w + 3) / 4;
     return g;
@@ -130,20 +133,20 @@ extern "C" int pair_emul_sweep(int w, int h, int d, const float* x, const float*
     const int Wp = w + 2;
     auto unpack = [&](const float* src, std::vector<float>& dst) {
         for (int z = 0; z <= d + 1; ++z) for (int y = 0; y <= h + 1; ++y) for (int xx = 0; xx <= w + 1; ++xx)
-            dst[(size_t)g.plane + fl_idx(g, xx, y, z)] = src[((size_t)z * g.rows + y) * Wp + xx];
+            dst[(size_t)(FL_ZPAD * g.plane) + fl_idx(g, xx, y, z)] = src[((size_t)z * g.rows + y) * Wp + xx];
     };
     unpack(x, fx); unpack(rhs, fr);
     fo = fx;                                               // the partner buffer starts as a copy (edges, corners)
     // zero bits as k_build_zbits makes them (solid: obs == 1; no-slip: an in-domain 6-neighbour is solid)
     const int pairs = (g.rows + 1) / 2;
-    std::vector<unsigned short> z0((size_t)(d + 2) * pairs * 32, 0), z1 = z0;
+    std::vector<unsigned short> z0((size_t)(d + 2 * FL_HALO) * pairs * 32, 0), z1 = z0;
     auto ob = [&](int xx, int y, int z) { return obs[((size_t)z * g.rows + y) * Wp + xx]; };
     for (int z = 1; z <= d; ++z) for (int y = 1; y <= h; ++y) for (int xx = 1; xx <= w; ++xx) {
         const bool solid = ob(xx, y, z) == 1.0f;
         const bool ns = !solid && ((xx + 1 <= w && ob(xx + 1, y, z) == 1.0f) || (xx - 1 >= 1 && ob(xx - 1, y, z) == 1.0f) ||
                                    (y + 1 <= h && ob(xx, y + 1, z) == 1.0f) || (y - 1 >= 1 && ob(xx, y - 1, z) == 1.0f) ||
                                    (z + 1 <= d && ob(xx, y, z + 1) == 1.0f) || (z - 1 >= 1 && ob(xx, y, z - 1) == 1.0f));
-        const size_t t = ((size_t)z * pairs + (y >> 1)) * 32 + (xx - 1) / 8;
+        const size_t t = ((size_t)(z + FL_HALO - 1) * pairs + (y >> 1)) * 32 + (xx - 1) / 8;
         const unsigned bit = 1u << (8 * (y & 1) + ((xx - 1) & 7));
         if (solid) z0[t] |= bit;
         if (solid || ns) z1[t] |= bit;
@@ -164,14 +167,14 @@ extern "C" int pair_emul_sweep(int w, int h, int d, const float* x, const float*
     A.g = g; A.a = a; A.c_recip = 1.0f / c; A.nty = nty;
     A.segs = segs.data(); A.seg_first = first.data();
     A.zbits[0] = z0.data(); A.zbits[1] = z1.data(); A.zb_pairs = pairs;
-    A.b[0] = b; A.dst[0] = fo.data() + g.plane;
-    A.map[0] = CUtensorMap{ fx.data(), { g.pitch, g.rows, g.Dl + 4 }, { g.pitch, g.plane }, { SW_BOXW, GE::BR } };
-    A.rmap[0] = CUtensorMap{ fr.data(), { g.pitch, g.rows, g.Dl + 4 }, { g.pitch, g.plane }, { SW_RBOXW, GE::TR } };
+    A.b[0] = b; A.dst[0] = fo.data() + FL_ZPAD * g.plane;
+    A.map[0] = CUtensorMap{ fx.data(), { g.pitch, g.rows, g.Dl + 2 + 2 * FL_ZPAD }, { g.pitch, g.plane }, { SW_BOXW, GE::BR } };
+    A.rmap[0] = CUtensorMap{ fr.data(), { g.pitch, g.rows, g.Dl + 2 + 2 * FL_ZPAD }, { g.pitch, g.plane }, { SW_RBOXW, GE::TR } };
     for (int bid = 0; bid + 1 < (int)first.size(); ++bid) {
         if (unroll == 6) { if (up) run_cta<true, 6>(A, bid); else run_cta<false, 6>(A, bid); }
         else             { if (up) run_cta<true, 2>(A, bid); else run_cta<false, 2>(A, bid); }
     }
     for (int z = 0; z <= d + 1; ++z) for (int y = 0; y <= h + 1; ++y) for (int xx = 0; xx <= w + 1; ++xx)
-        out[((size_t)z * g.rows + y) * Wp + xx] = fo[(size_t)g.plane + fl_idx(g, xx, y, z)];
+        out[((size_t)z * g.rows + y) * Wp + xx] = fo[(size_t)(FL_ZPAD * g.plane) + fl_idx(g, xx, y, z)];
     return 0;
 }

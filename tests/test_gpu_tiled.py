@@ -134,15 +134,17 @@ def test_headline_grid_vs_oracle_full_depth():
     assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, "256^3 airfoil, 1 iteration, acc 4 [rb]")
 
 
-# shapes the temporally blocked kernel takes (two sweeps per pass, csrc/sweep_pair*.cuh: 128 < W <= 256,
-# W % 8 == 0, H even); odd sweep counts finish with one ordinary sweep
+# shapes the temporally blocked kernel takes when FLUID_PAIR=1 (two sweeps per pass, csrc/sweep_pair*.cuh:
+# 128 < W <= 256, W % 8 == 0, H even); odd sweep counts finish with one ordinary sweep
 PAIR_SHAPES = [(136, 12, 7), (256, 24, 9), (200, 10, 5), (144, 2, 3), (256, 64, 33), (248, 30, 40), (160, 16, 1),
                (256, 256, 12)]
 
 
+@pytest.mark.parametrize("unroll", ["2", "6"])
 @pytest.mark.parametrize("w,h,d", PAIR_SHAPES)
 @pytest.mark.parametrize("b,acc", [(0, 3), (1, 2), (2, 5), (3, 4)])
-def test_pair_linear_solver(w, h, d, b, acc):
+def test_pair_linear_solver(monkeypatch, w, h, d, b, acc, unroll):
+    monkeypatch.setenv("FLUID_PAIR", "1"); monkeypatch.setenv("FLUID_PAIR_UNROLL", unroll)
     gpu, cpu = pair(w, h, d, acc, 0x0, ORDER_RB)
     gpu.linearSolver(b, "v_y", "v_y_prev", 0.37, 3.22); cpu.linear_solver(b, "v_y", "v_y_prev", 0.37, 3.22)
     assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, f"pair-sweep linearSolver {w}x{h}x{d} b={b} acc={acc}")
@@ -150,21 +152,23 @@ def test_pair_linear_solver(w, h, d, b, acc):
 
 @pytest.mark.parametrize("zc", [1, 2, 3, 7])
 def test_pair_chunk_sizes(monkeypatch, zc):
-    monkeypatch.setenv("FLUID_TILED_ZC", str(zc))
+    monkeypatch.setenv("FLUID_TILED_ZC", str(zc)); monkeypatch.setenv("FLUID_PAIR", "1")
     gpu, cpu = pair(256, 36, 11, 4, 0x0, ORDER_RB)
     gpu.linearSolver(3, "v_z", "v_z_prev", 1.0, 6.0); cpu.linear_solver(3, "v_z", "v_z_prev", 1.0, 6.0)
     assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, f"pair-sweep zc={zc}")
 
 
 def test_pair_equals_single_sweeps(monkeypatch):
-    """A/B inside the library: FLUID_NO_PAIR=1 routes the same solve through k_sweep_stream (one sweep per
-    pass); whole run() iterations must come out bit-identical either way."""
+    """A/B inside the library: FLUID_PAIR=1 routes the solves through k_sweep_pair (two sweeps per pass, with
+    the 4-field diffusion launch, the buffer swap and an odd sweep count), the default through k_sweep_stream
+    (one sweep per pass); whole run() iterations must come out bit-identical either way."""
     from fluid_simulation_b200 import Simulation, masks
     w, h, d, acc = 256, 128, 48, 7
     obs = masks.airfoil(w, h, d)
+    monkeypatch.setenv("FLUID_PAIR", "1")
     a = Simulation(w, h, d, 1, acc=acc)
     a.set("obs", obs); a.run_iterations(2)
-    monkeypatch.setenv("FLUID_NO_PAIR", "1")
+    monkeypatch.delenv("FLUID_PAIR")
     b = Simulation(w, h, d, 1, acc=acc)
     b.set("obs", obs); b.run_iterations(2)
     assert_bitwise(a.state(), b.state(), FIELD_NAMES, "pair vs single sweeps")
