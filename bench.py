@@ -304,6 +304,12 @@ def run_ours(args):
     # ---- end to end through the reference-facing API with HOST buffers -----------------------
     e2e = run_e2e(sim, args, w, h, d, mask, barrier, reduce_max, rank, world)
 
+    # ---- the other configurations north_star names, measured in the same (driver-run) process -----
+    extra = None
+    if not args.no_extra and (w, h, acc, args.strong) == (W0, H0, ACC0, False):
+        sim.close()
+        extra = run_extra(rank, world, dist, local)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
@@ -324,16 +330,69 @@ def run_ours(args):
                        "parallelism": f"z-slab x{world}" if world > 1 else "1 GPU",
                        "l2": "state (11 fields, %.0f MB) exceeds the 126 MB L2" % (11 * 4 * local_cells / 1e6)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-            "cpu_baseline": cpu, "slab_parity": slab_parity,
+            "cpu_baseline": cpu, "slab_parity": slab_parity, "extra": extra,
             "stats": {k: float(v) for k, v in stats.items()},
         }
         print(json.dumps(line), flush=True)
-    sim.close()
+    if extra is None:
+        sim.close()
     if dist is not None:
         dist.destroy_process_group()
     if slab_parity is not None and not slab_parity["bit_identical"]:
         return 3                                          # a fast wrong answer is not a result
     return 0
+
+
+def run_extra(rank, world, dist, local):
+    """BASELINE.json's scaling configurations, device-timed like `value` (CUDA events, max over ranks), a few
+    steps each so that the whole bench still ends within minutes:
+      configs[3]  512^3 tunnel, acc 80, split over the N ranks (strong scaling; N = 1 is the base of the curve)
+      configs[4]  1024 x 512 x 512, acc 200, 8 ranks, with the frame dump every 10 steps (pinned async D2H)
+      target      1024^3, acc 80, 8 ranks, beside 1024 x 1024 x 128 on one GPU (the base of its efficiency)."""
+    from fluid_simulation_b200 import Simulation, masks, multi_gpu, SOLVER_RB
+    out = {}
+
+    def timed(tag, w, h, d, acc, steps, warm, dump_every=0):
+        sim = Simulation(w, h, d, steps, acc=acc, flags=SOLVER_RB, rank=rank, nranks=world)
+        if world > 1:
+            multi_gpu.attach(sim, dist)
+        sim.set("obs", masks.airfoil_planes(w, h, d, sim.z_lo - 4, sim.d_local + 8))
+        sim.run_iterations(warm)
+        if dump_every:
+            sim.dump_frame_async(); sim.frame_wait()       # pinned buffers exist before the clock starts
+        sim.sync()
+        if dist is not None:
+            dist.barrier()
+        t0 = time.perf_counter()
+        sim.timer_start()
+        for i in range(steps):
+            sim.run_iterations(1)
+            if dump_every and (i + 1) % dump_every == 0:
+                sim.dump_frame_async()
+        ms = sim.timer_stop()
+        if dump_every:
+            sim.frame_wait()
+        wall = (time.perf_counter() - t0) * 1e3
+        if dist is not None:
+            import torch
+            t = torch.tensor([ms, wall], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, wall = float(t[0]), float(t[1])
+        sim.close()
+        r = {"grid": f"{w}x{h}x{d}", "acc": acc, "n_gpus": world, "steps": steps, "ms_per_step": ms / steps,
+             "glups": w * h * d * steps / (ms * 1e-3) / 1e9}
+        if dump_every:
+            r.update({"dump_every": dump_every, "ms_per_step_with_dumps_wall": wall / steps,
+                      "frame_bytes": 5 * 4 * (w + 2) * (h + 2) * (d + 2)})
+        out[tag] = r
+
+    timed("configs3_512cubed_strong", 512, 512, 512, 80, 3, 1)
+    if world == 1:
+        timed("base_1024x1024x128_one_gpu", 1024, 1024, 128, 80, 2, 1)
+    if world == 8:
+        timed("configs4_1024x512x512_acc200_dump10", 1024, 512, 512, 200, 10, 1, dump_every=10)
+        timed("target_1024cubed", 1024, 1024, 1024, 80, 2, 1)
+    return out
 
 
 def run_slab_parity(rank, world, dist):
@@ -417,6 +476,7 @@ def main():
     ap.add_argument("--solver", default="rb", choices=["rb", "jacobi"])
     ap.add_argument("--elide", action="store_true", help="skip the dead density diffusion (F2)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra scaling configurations (512^3 strong, ...)")
     ap.add_argument("--w", type=int); ap.add_argument("--h", type=int); ap.add_argument("--d", type=int)
     ap.add_argument("--acc", type=int)
     ap.add_argument("--size", help="WxHxD, same as --w/--h/--d (whose short names torchrun's own parser trips over)")

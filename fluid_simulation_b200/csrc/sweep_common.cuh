@@ -26,18 +26,17 @@ __device__ __forceinline__ void   sw_sts4(float* p, float4 v) { *reinterpret_cas
 #define SW_ZLO 16u
 #define SW_ZHI 32u
 
-// the setBounds epilogue for one finished quad (simulation.cpp:183-246), see fl_store_bounded:
-// ghosts take the PRE-zero value, then solids (and, for velocity components, cells touching a
-// solid) are zeroed.
-__device__ __forceinline__ void sw_store(const Grid& g, float* __restrict__ out, long long c, const float4& raw,
-                                         unsigned f4, int b, unsigned zmask4, unsigned edge)
+// the setBounds epilogue for one finished quad (simulation.cpp:183-246), see fl_store_bounded: ghosts take the
+// PRE-zero value, then solids (and, for velocity components, cells touching a solid) are zeroed;
+// bit i of `bits` = "cell i of the quad becomes 0"
+__device__ __forceinline__ void sw_store_bits(const Grid& g, float* __restrict__ out, long long c, const float4& raw,
+                                              unsigned bits, int b, unsigned edge)
 {
-    const unsigned t = f4 & zmask4;
     float4 v;
-    v.x = (t & 0x000000ffu) ? 0.0f : raw.x;
-    v.y = (t & 0x0000ff00u) ? 0.0f : raw.y;
-    v.z = (t & 0x00ff0000u) ? 0.0f : raw.z;
-    v.w = (t & 0xff000000u) ? 0.0f : raw.w;
+    v.x = (bits & 1u) ? 0.0f : raw.x;
+    v.y = (bits & 2u) ? 0.0f : raw.y;
+    v.z = (bits & 4u) ? 0.0f : raw.z;
+    v.w = (bits & 8u) ? 0.0f : raw.w;
     st4(out + c, v);
     if (edge) {
         if (edge & SW_XLO) out[c - 1] = (b == 1) ? -raw.x : raw.x;            // :189
@@ -54,4 +53,3 @@ __device__ __forceinline__ void sw_store(const Grid& g, float* __restrict__ out,
         }
     }
 }
-

@@ -6,52 +6,6 @@
 
 #define SP_SEGCOST 8                     // extra pipeline steps per segment (6 fill / drain + prologue)
 
-// One bit per cell: "setBounds zeroes this cell" for scalars ([0]: solid) and for velocity components
-// ([1]: solid or touching a solid), simulation.cpp:219-245.  Layout: one 16-bit word per (plane, row pair,
-// lane), local planes 1-FL_HALO .. Dl+FL_HALO: bits 0-7 = cells 1 + 8*lane .. + 7 of row 2*pair, bits 8-15 = the
-// same cells of row 2*pair + 1.
-// 2 x 2 MB at 256^3: the sweeps read them from L2 instead of 1 byte per cell from HBM.
-__global__ void __launch_bounds__(256) k_build_zbits(Grid g, const unsigned char* __restrict__ flags,
-                                                     unsigned short* __restrict__ z0, unsigned short* __restrict__ z1, int pairs)
-{
-    const long long n = (long long)(g.Dl + 2 * FL_HALO) * pairs * 32;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
-        const int lane = (int)(t & 31);
-        const long long r = t >> 5;
-        const int pr = (int)(r % pairs), zl = (int)(r / pairs) - (FL_HALO - 1);
-        unsigned s0 = 0u, s1 = 0u;
-        // the flag volume is non-zero exactly where a cell of the tunnel's interior is held with its z-neighbours
-        if (zl >= 2 - FL_HALO && zl <= g.Dl + FL_HALO - 1)
-            for (int k = 0; k < 2; ++k) {
-                const int y = 2 * pr + k;
-                if (y < 1 || y > g.H) continue;
-                for (int i = 0; i < 8; ++i) {
-                    const int x = 1 + 8 * lane + i;
-                    if (x > g.W) break;
-                    const unsigned f = flags[fl_idx(g, x, y, zl)];
-                    if (f & FL_SOLID) s0 |= 1u << (8 * k + i);
-                    if (f & (FL_SOLID | FL_NOSLIP)) s1 |= 1u << (8 * k + i);
-                }
-            }
-        z0[t] = (unsigned short)s0; z1[t] = (unsigned short)s1;
-    }
-}
-
-struct PairState {                       // hangs off StreamState::pair
-    unsigned short* zbits[2] = { nullptr, nullptr };
-    int pairs = 0;
-    unsigned long long flags_version = ~0ull;      // version of the flag volume the bits were built from
-};
-
-void sw_pair_release(StreamState* s)
-{
-    PairState* ps = (PairState*)s->pair;
-    if (!ps) return;
-    cudaFree(ps->zbits[0]); cudaFree(ps->zbits[1]);
-    delete ps;
-    s->pair = nullptr;
-}
-
 // FLUID_PAIR=1 switches the temporally blocked kernel on.  It is OFF by default: measured on B200 at 256^3 it
 // halves the HBM traffic per sweep (140 instead of 242 MB, ncu) but is bound by instruction issue at 8 warps
 // per SM and ends up level with k_sweep_stream (47.7 vs 46.5 us per single-field sweep, 44.6 vs 42.9 us in the
@@ -79,27 +33,13 @@ inline int sw_pair_run(fluid_handle* h, int nb, const int* b, const int* fid, co
     SwPlan plan;
     if (int e = sw_get_plan(h, nb, GE::TY, 1, 0, &plan, SP_SEGCOST)) return e;
 
-    // zero bits, rebuilt whenever the flag volume was
-    if (!s->pair) s->pair = new PairState();
-    PairState* ps = (PairState*)s->pair;
-    if (!ps->zbits[0]) {
-        ps->pairs = (g.rows + 1) / 2;
-        const size_t n = (size_t)(g.Dl + 2 * FL_HALO) * ps->pairs * 32 * sizeof(unsigned short);
-        FL_CUDA(h, cudaMalloc(&ps->zbits[0], n));
-        FL_CUDA(h, cudaMalloc(&ps->zbits[1], n));
-    }
-    if (ps->flags_version != h->flags_version) {
-        const long long n = (long long)(g.Dl + 2 * FL_HALO) * ps->pairs * 32;
-        k_build_zbits<<<fl_grid_1d(n), 256, 0, h->stream>>>(g, h->cflags, ps->zbits[0], ps->zbits[1], ps->pairs);
-        FL_CHECK_LAUNCH(h);
-        ps->flags_version = h->flags_version;
-    }
+    if (int e = sw_get_zbits(h)) return e;                                // zero bits, rebuilt whenever the flag volume was
 
     PairArgs A;
     A.g = g; A.a = a; A.c_recip = 1.0f / c;                              // simulation.cpp:257
     A.nty = (g.H + GE::TY - 1) / GE::TY;
     A.segs = plan.segs; A.seg_first = plan.seg_first;
-    A.zbits[0] = ps->zbits[0]; A.zbits[1] = ps->zbits[1]; A.zb_pairs = ps->pairs;
+    A.zbits[0] = s->zbits[0]; A.zbits[1] = s->zbits[1]; A.zb_pairs = s->zb_pairs;   // zb_lanes == 32 (W <= 256)
 
     float* cur[4]; float* alt[4];
     if (nb == 4 && !h->scratch[3]) {                                      // fourth ping-pong partner, first use

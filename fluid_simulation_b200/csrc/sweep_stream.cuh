@@ -37,7 +37,8 @@ struct alignas(64) StreamArgs {
     CUtensorMap rmap[4];                 // its right-hand side (box SW_RBOXW x BR-2 x 1)
     float* dst[4];
     int b[4];
-    const unsigned char* flags;
+    const unsigned short* zbits[2];      // zero bits, one per cell ([0]: solid, [1]: solid | no-slip), see k_build_zbits
+    unsigned zb_plane; int zb_lanes;     // words per plane / per row pair of that volume
     const SwSeg* segs;                   // CTA k works through segs[seg_first[k] .. seg_first[k+1])
     const int* seg_first;
     Grid g;
@@ -164,7 +165,8 @@ struct SwGeom {
 // follow the same indexing.
 struct SwThread {
     float4 QA[4], QB[4], RA[4], RB[4];
-    unsigned FA[4], FB[4];
+    unsigned FA[4];                        // zero-bit words (row A: bits 0-7, row B: bits 8-15 of the thread's octet)
+    const unsigned short* zbv; unsigned zoff; int zsh;   // this segment's bit volume, the thread's word in a plane, its nibble
     unsigned oA, oB;                       // element offsets of the two quads in plane p+1
     int offA, offB;                        // shared-memory offsets of the two x quads inside a slot
     int roffA, roffB;                      // ... and of the two rhs quads
@@ -193,7 +195,7 @@ __device__ __forceinline__ float4 sw_lds4_half(const float* p, unsigned& sink)
 // of the reference (z+1 before z-1) is kept in both directions.
 template <int BOXF, int XSLOTF, int MODE, int DIR, int U, int E>
 __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float* __restrict__ out, int b,
-                                        unsigned zmask4, int p, int za, int zb, bool has_next,
+                                        int p, int za, int zb, bool has_next,
                                         const float* Up, const float* Un, unsigned long long* bar_n,
                                         unsigned phase_n, float* vbuf)
 {
@@ -205,8 +207,7 @@ __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float*
     // flag bytes two steps ahead (t.oA addresses the next plane): consumed by the store of that
     // plane, which is three steps away for red-black and two for Jacobi
     if (p + 2 * DIR >= za && p + 2 * DIR <= zb) {
-        t.FA[I2] = *reinterpret_cast<const unsigned*>(A.flags + (t.oA + dplane));
-        t.FB[I2] = *reinterpret_cast<const unsigned*>(A.flags + (t.oB + dplane));
+        t.FA[I2] = t.zbv[(unsigned)(p + 2 * DIR + FL_HALO - 1) * A.zb_plane + t.zoff];
     }
     // Every shared-memory operand of the step is fetched up front, in one burst, so that the LDS
     // latency is exposed once per plane instead of once per stage: rhs and the row neighbours of plane
@@ -252,11 +253,11 @@ __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float*
             float4 e = cA, f = cA;
             sw_relax2<0>(e, LA, RA, cB, ymA, zpA0, zmA0, t.RA[IC], a, cr);
             sw_relax2<1>(f, LA, RA, cB, ymA, zpA0, zmA0, t.RA[IC], a, cr);
-            if (t.ownA) sw_store(g, out, t.oA - dplane, make_float4(e.x, f.y, e.z, f.w), t.FA[IC], b, zmask4, t.eA | zbits);
+            if (t.ownA) sw_store_bits(g, out, t.oA - dplane, make_float4(e.x, f.y, e.z, f.w), t.FA[IC] >> t.zsh, b, t.eA | zbits);
             e = cB; f = cB;
             sw_relax2<0>(e, LB, RB, ypB, cA, zpB0, zmB0, t.RB[IC], a, cr);
             sw_relax2<1>(f, LB, RB, ypB, cA, zpB0, zmB0, t.RB[IC], a, cr);
-            if (t.ownB) sw_store(g, out, t.oB - dplane, make_float4(e.x, f.y, e.z, f.w), t.FB[IC], b, zmask4, t.eB | zbits);
+            if (t.ownB) sw_store_bits(g, out, t.oB - dplane, make_float4(e.x, f.y, e.z, f.w), t.FA[IC] >> (8 + t.zsh), b, t.eB | zbits);
         }
     } else {
         // ---- stage 0: colour-0 cells of plane p, in registers --------------------------------------
@@ -294,8 +295,8 @@ __device__ __forceinline__ void sw_step(SwThread& t, const StreamArgs& A, float*
             }
             const int gzq = g.zlo + q - 1;
             const unsigned zbits = (gzq == 1 ? SW_ZLO : 0u) | (gzq == g.D ? SW_ZHI : 0u);
-            if (t.ownA && !(A.dbg & 1)) sw_store(g, out, t.oA - 2u * dplane, tA, t.FA[IM], b, zmask4, t.eA | zbits);
-            if (t.ownB && !(A.dbg & 1)) sw_store(g, out, t.oB - 2u * dplane, tB, t.FB[IM], b, zmask4, t.eB | zbits);
+            if (t.ownA && !(A.dbg & 1)) sw_store_bits(g, out, t.oA - 2u * dplane, tA, t.FA[IM] >> t.zsh, b, t.eA | zbits);
+            if (t.ownB && !(A.dbg & 1)) sw_store_bits(g, out, t.oB - 2u * dplane, tB, t.FA[IM] >> (8 + t.zsh), b, t.eB | zbits);
         }
     }
 }
@@ -389,7 +390,6 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     const int first = has_behind ? ps - DIR : ps;                // first plane loaded, then first + DIR, ...
     const int nplanes = (DIR > 0 ? hi - first : first - lo) + 1;
     const int b = A.b[batch];
-    const unsigned zmask4 = fl_zero_mask(b) * 0x01010101u;
     float* __restrict__ out = A.dst[batch];
     if ((sg.mode >> 1) && !(A.dbg & 4)) sw_await_face(A, (sg.mode >> 1) - 1, tid);     // dbg 4: timing experiment, results invalid
 
@@ -424,8 +424,13 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     // grid read a harmless in-range cell instead of being predicated off.
     t.oA = (t.intA ? (unsigned)fl_idx(g, x0, yA, 0) : safe) + (unsigned)ps * plane;
     t.oB = (t.intB ? (unsigned)fl_idx(g, x0, yB, 0) : safe) + (unsigned)ps * plane;
+    {   // the thread's zero-bit word: row pair yA / 2 (yA is even), octet of the quad; clamped for rows / lanes outside the grid
+        const int pairs = (int)(A.zb_plane / (unsigned)A.zb_lanes);
+        const int zp = min(max(yA, 0) >> 1, pairs - 1), zo = min((x0 - 1) >> 3, A.zb_lanes - 1);
+        t.zbv = A.zbits[b == 0 ? 0 : 1]; t.zoff = (unsigned)(zp * A.zb_lanes + zo); t.zsh = ((x0 - 1) >> 2 & 1) * 4;
+    }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { t.QA[i] = zero4; t.QB[i] = zero4; t.RA[i] = zero4; t.RB[i] = zero4; t.FA[i] = 0; t.FB[i] = 0; }
+    for (int i = 0; i < 4; ++i) { t.QA[i] = zero4; t.QB[i] = zero4; t.RA[i] = zero4; t.RB[i] = zero4; t.FA[i] = 0; }
 
     // prologue: own column of the plane behind ps (ring index 1) and of ps (index 2); flag bytes
     // of the first plane that is stored
@@ -438,8 +443,7 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     if (has_behind) { const float* Ub = consume(); t.QA[1] = sw_lds4(Ub + t.offA); t.QB[1] = sw_lds4(Ub + t.offB); }
     const float* Up = consume();
     t.QA[2] = sw_lds4(Up + t.offA); t.QB[2] = sw_lds4(Up + t.offB);
-    t.FA[3] = *reinterpret_cast<const unsigned*>(A.flags + (t.oA + dplane));
-    t.FB[3] = *reinterpret_cast<const unsigned*>(A.flags + (t.oB + dplane));
+    t.FA[3] = t.zbv[(unsigned)(ps + DIR + FL_HALO - 1) * A.zb_plane + t.zoff];
     __syncthreads();        // the slot of the plane behind ps is re-armed by the first step
 
     int p = ps, step = 0;
@@ -459,7 +463,7 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
         const unsigned ph_n = ph_con;                                                                   \
         const float* Un = uring + s_con * SLOTF;                                                        \
         if (has_next) { if (++s_con == NSLOT) { s_con = 0; ph_con ^= 1u; } }                            \
-        sw_step<BOXF, XSLOTF, MODE, DIR, U, E>(t, A, out, b, zmask4, p, za, zb, has_next, Up, Un, bar_n, \
+        sw_step<BOXF, XSLOTF, MODE, DIR, U, E>(t, A, out, b, p, za, zb, has_next, Up, Un, bar_n,         \
                                                ph_n, vbuf);                                             \
         Up = Un; p += DIR; ++step; ++jc;                                                                \
         __syncthreads();                                                                                \
@@ -559,7 +563,8 @@ struct StreamState {
     bool face_cta = true;                                       // separate edge CTAs (plan part 4); FLUID_SW_FACE_CTA=0: hand-over inside ordinary segments (part 5)
     int edge = SW_EDGE_DEFAULT;                                 // planes per edge segment at an interior slab face (>= 2)
     int plan_mode = 2, plan_min_fill = 85;
-    void* pair = nullptr;                                       // PairState (sweep_pair.cuh)
+    // zero-bit volume (k_build_zbits): rebuilt whenever the flag volume was
+    unsigned short* zbits[2] = { nullptr, nullptr }; int zb_pairs = 0, zb_lanes = 0; unsigned long long zb_version = ~0ull;
     int pdl = 1;                                                // FLUID_SW_PDL: programmatic dependent launch between the sweeps of a solve; 0 = off, 1 = on one GPU (measured: 22.78 -> 22.41 ms per 256^3 step), 2 = on z-slabs too                      // FLUID_SW_PLAN: 0 = auto, 1 = uniform ranges, 2 = balanced budget
 };
 
@@ -588,7 +593,6 @@ inline StreamState* sw_state(fluid_handle* h)
     return (StreamState*)h->tiled;
 }
 
-void sw_pair_release(StreamState* s);                              // sweep_pair.cuh
 int fl_pair_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid, float a, float c,
                   unsigned x_from_rhs, int* done);
 
@@ -596,9 +600,61 @@ inline void fl_tiled_release(fluid_handle* h)
 {
     StreamState* s = (StreamState*)h->tiled;
     if (s) for (auto& kv : s->plans) { cudaFree(kv.second.segs); cudaFree(kv.second.seg_first); }
-    if (s) sw_pair_release(s);
+    if (s) { cudaFree(s->zbits[0]); cudaFree(s->zbits[1]); }
     delete s;
     h->tiled = nullptr;
+}
+
+// One bit per cell: "setBounds zeroes this cell" for scalars ([0]: solid) and for velocity components
+// ([1]: solid or touching a solid), simulation.cpp:219-245.  Layout: one 16-bit word per (local plane
+// 1-FL_HALO .. Dl+FL_HALO, row pair, octet): bits 0-7 = cells 1 + 8*octet .. + 7 of row 2*pair, bits 8-15 = the
+// same cells of row 2*pair + 1.  2 x 2 MB at 256^3: the sweeps read them from L2 instead of one flag byte per
+// cell from HBM (19.8 MB per field-sweep at 256^3).
+__global__ void __launch_bounds__(256) k_build_zbits(Grid g, const unsigned char* __restrict__ flags,
+                                                     unsigned short* __restrict__ z0, unsigned short* __restrict__ z1,
+                                                     int pairs, int lanes)
+{
+    const long long n = (long long)(g.Dl + 2 * FL_HALO) * pairs * lanes;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const int oct = (int)(t % lanes);
+        const long long r = t / lanes;
+        const int pr = (int)(r % pairs), zl = (int)(r / pairs) - (FL_HALO - 1);
+        unsigned s0 = 0u, s1 = 0u;
+        // the flag volume is non-zero exactly where a cell of the tunnel's interior is held with its z-neighbours
+        if (zl >= 2 - FL_HALO && zl <= g.Dl + FL_HALO - 1)
+            for (int k = 0; k < 2; ++k) {
+                const int y = 2 * pr + k;
+                if (y < 1 || y > g.H) continue;
+                for (int i = 0; i < 8; ++i) {
+                    const int x = 1 + 8 * oct + i;
+                    if (x > g.W) break;
+                    const unsigned f = flags[fl_idx(g, x, y, zl)];
+                    if (f & FL_SOLID) s0 |= 1u << (8 * k + i);
+                    if (f & (FL_SOLID | FL_NOSLIP)) s1 |= 1u << (8 * k + i);
+                }
+            }
+        z0[t] = (unsigned short)s0; z1[t] = (unsigned short)s1;
+    }
+}
+
+inline int sw_get_zbits(fluid_handle* h)
+{
+    StreamState* s = sw_state(h);
+    const Grid& g = h->g;
+    if (!s->zbits[0]) {
+        s->zb_pairs = (g.rows + 1) / 2;
+        s->zb_lanes = ((g.W + 7) / 8 + 31) / 32 * 32;
+        const size_t n = (size_t)(g.Dl + 2 * FL_HALO) * s->zb_pairs * s->zb_lanes * sizeof(unsigned short);
+        FL_CUDA(h, cudaMalloc(&s->zbits[0], n));
+        FL_CUDA(h, cudaMalloc(&s->zbits[1], n));
+    }
+    if (s->zb_version != h->flags_version) {
+        const long long n = (long long)(g.Dl + 2 * FL_HALO) * s->zb_pairs * s->zb_lanes;
+        k_build_zbits<<<fl_grid_1d(n), 256, 0, h->stream>>>(g, h->cflags, s->zbits[0], s->zbits[1], s->zb_pairs, s->zb_lanes);
+        FL_CHECK_LAUNCH(h);
+        s->zb_version = h->flags_version;
+    }
+    return 0;
 }
 
 inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows, CUtensorMap* out)
@@ -809,7 +865,9 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     if (int e = sw_get_plan(h, nb, GE::TY, CPS, fused ? (s->face_cta ? 4 : 5) : overlap ? 2 : 0, &plan)) return e;
     if (overlap && !fused) if (int e = sw_get_plan(h, nb, GE::TY, CPS, 1, &plan_edge)) return e;
     StreamArgs A;
-    A.g = g; A.a = a; A.c_recip = 1.0f / c; A.flags = h->cflags;         // simulation.cpp:257
+    A.g = g; A.a = a; A.c_recip = 1.0f / c;                              // simulation.cpp:257
+    if (int e = sw_get_zbits(h)) return e;
+    A.zbits[0] = s->zbits[0]; A.zbits[1] = s->zbits[1]; A.zb_lanes = s->zb_lanes; A.zb_plane = (unsigned)(s->zb_pairs * s->zb_lanes);
     A.nty = (g.H + GE::TY - 1) / GE::TY;
     A.segs = plan.segs; A.seg_first = plan.seg_first;
     A.dbg = s->dbg;

@@ -286,21 +286,30 @@ class Simulation:
 
     # -- frame dumps (simulation.cpp:56-60, 140-148) ------------------------------------------
     def _ensure_frame_bufs(self):
+        """Five pinned host buffers for (dens, obs, v_x, v_y, v_z), each holding the padded planes this rank OWNS
+        (the whole frame on one GPU; a z-slab's share of it otherwise, so that eight ranks of a 1024 x 512 x 512
+        run pin 0.7 GB each instead of 5.4 GB)."""
         if self._frame_bufs is None:
+            first, count = self._owned_planes()
+            plane = self.shape[1] * self.shape[2]
             bufs = []
             for _ in range(5):
-                ptr = self._L.fluid_host_alloc(self.size * 4)
+                ptr = self._L.fluid_host_alloc(count * plane * 4)
                 if not ptr:
                     raise FluidError("pinned host allocation failed")
-                arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float)), shape=(self.size,))
-                bufs.append((arr.reshape(self.shape), ptr))
+                arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float)), shape=(count * plane,))
+                bufs.append((arr.reshape((count,) + self.shape[1:]), ptr))
             self._frame_bufs = bufs
         return self._frame_bufs
 
     def dump_frame_async(self, which=(True, True, True, True, True)):
-        """Start the async D2H of (dens, obs, v_x, v_y, v_z) into pinned buffers; returns the views."""
+        """Start the async D2H of (dens, obs, v_x, v_y, v_z) into pinned buffers; returns the views (this rank's
+        owned planes, `_owned_planes()[0]` first)."""
         bufs = self._ensure_frame_bufs()
-        ptrs = (C.c_void_p * 5)(*[ptr if w else None for (_, ptr), w in zip(bufs, which)])
+        first, _ = self._owned_planes()
+        # the C ABI takes the base of a whole-frame buffer and writes this rank's planes at their offset in it
+        skew = first * self.shape[1] * self.shape[2] * 4
+        ptrs = (C.c_void_p * 5)(*[(ptr - skew) if w else None for (_, ptr), w in zip(bufs, which)])
         self._ck(self._L.fluid_dump_frame_async(self._h, ptrs))
         return [a for a, _ in bufs]
 
@@ -345,7 +354,7 @@ class Simulation:
                 plane_bytes = self.shape[1] * self.shape[2] * 4
                 off = self._frames_written * self.size * 4 + first * plane_bytes
                 for f, (arr, _) in zip(self._frame_files, self._frame_bufs):
-                    os.pwrite(f.fileno(), arr[first:first + count].tobytes(), off)
+                    os.pwrite(f.fileno(), arr.tobytes(), off)
             self._frames_written = getattr(self, "_frames_written", 0) + 1
             self._frame_pending = False
 

@@ -78,7 +78,8 @@ fluid_handle* fluid_create(int w, int h, int d, int speed, float dt, float diff,
 
 /* z-slab member of a multi-GPU run: this process owns global planes z_lo..z_lo+d_local-1 of a
  * w x h x d tunnel (the reference has no distributed mode).  `rank`/`nranks` order the
- * slabs along z (equal slabs, remainder planes to the low ranks; d >= 2*nranks).  Before the first
+ * slabs along z (equal slabs, remainder planes to the low ranks; d >= 4*nranks: a slab keeps four halo
+ * planes per interior side and every slab must hold at least as many).  Before the first
  * device operation the host program attaches the communicator (fluid_comm_init) and maps the peers'
  * advection sources (fluid_ipc_export / fluid_ipc_import); see fluid_simulation_b200/multi_gpu.py. */
 fluid_handle* fluid_create_slab(int w, int h, int d, int speed, float dt, float diff, float visc,

@@ -29,9 +29,9 @@ def test_halo_plan_is_symmetric():
     for r in range(n - 1):
         up, down = slab.halo_plan(d, n, r)["up"], slab.halo_plan(d, n, r + 1)["down"]
         assert up["peer"] == r + 1 and down["peer"] == r
-        assert len(up["send_planes"]) == len(down["recv_planes"]) == 2
+        assert len(up["send_planes"]) == len(down["recv_planes"]) == slab.HALO == 4
         dl = slab.halo_plan(d, n, r)["d_local"]
-        assert up["send_planes"] == (dl - 1, dl) and down["recv_planes"] == (-1, 0)
+        assert up["send_planes"] == (dl - 3, dl - 2, dl - 1, dl) and down["recv_planes"] == (-3, -2, -1, 0)
     assert slab.halo_plan(d, n, 0)["down"] is None and slab.halo_plan(d, n, n - 1)["up"] is None
 
 
@@ -86,29 +86,30 @@ def _worker(rank, world, port, q):
                     assert key not in lib.imported
                 else:
                     assert lib.imported[key] == bytes([peer * 16 + FIELDS[name]]) * 64
-        # 3. two-plane halo exchange of a global array, numpy emulation of fl_halo_exchange
-        d, hgt, w = 11, 4, 5
+        # 3. four-plane halo exchange of a global array, numpy emulation of fl_halo_exchange
+        d, hgt, w = 4 * world + 3, 4, 5
         glob = np.arange((d + 2) * hgt * w, dtype=np.float32).reshape(d + 2, hgt, w)
         plan = slab.halo_plan(d, world, rank)
         z0, dl = plan["z_lo"], plan["d_local"]
-        local = np.full((dl + 4, hgt, w), -1.0, np.float32)            # local planes -1 .. dl+2 -> index +1
-        local[2:dl + 2] = glob[z0:z0 + dl]                              # owned interior planes only
+        HP = slab.HALO - 1
+        local = np.full((dl + 2 * slab.HALO, hgt, w), -1.0, np.float32)   # local planes -3 .. dl+4 -> index +3
+        local[HP + 1:dl + HP + 1] = glob[z0:z0 + dl]                    # owned interior planes only
         import torch
         reqs = []
         for side in ("down", "up"):
             p = plan[side]
             if p is None:
                 continue
-            send = torch.from_numpy(np.ascontiguousarray(local[p["send_planes"][0] + 1:p["send_planes"][1] + 2]))
+            send = torch.from_numpy(np.ascontiguousarray(local[p["send_planes"][0] + HP:p["send_planes"][-1] + HP + 1]))
             recv = torch.empty_like(send)
             reqs.append((dist.isend(send, p["peer"]), dist.irecv(recv, p["peer"]), recv, p))
         for s, r, recv, p in reqs:
             s.wait(); r.wait()
-            local[p["recv_planes"][0] + 1:p["recv_planes"][1] + 2] = recv.numpy()
-        for zl in range(-1, dl + 3):
+            local[p["recv_planes"][0] + HP:p["recv_planes"][-1] + HP + 1] = recv.numpy()
+        for zl in range(-HP, dl + slab.HALO + 1):
             gz = z0 + zl - 1
             if 1 <= gz <= d and not (1 <= zl <= dl):                    # a halo plane interior to the tunnel
-                assert np.array_equal(local[zl + 1], glob[gz]), (rank, zl)
+                assert np.array_equal(local[zl + HP], glob[gz]), (rank, zl)
         # 4. statistics fold
         st = multi_gpu.reduce_stats(dist, {"dens_sum": 1.0 + rank, "dens_min": -rank, "dens_max": rank})
         assert st == {"dens_sum": sum(1.0 + r for r in range(world)), "dens_min": -(world - 1), "dens_max": world - 1}
