@@ -104,10 +104,10 @@ int fluid_ipc_import(fluid_handle* h, int peer_rank, int alloc_id, const char in
     // permutes alike: the peer's buffer with id i keeps corresponding to this rank's alloc_base[i].
     int slot = alloc_id;
     if (alloc_id < FLUID_NFIELDS)
-        for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
+        for (int i = 0; i < FLUID_NFIELDS + 4; ++i)
             if (h->alloc_base[i] == h->field[alloc_id] - FL_ZPAD * h->g.plane) slot = i;
     if (alloc_id >= FLUID_IPC_SCRATCH0 && alloc_id < FLUID_IPC_SYNC)
-        for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
+        for (int i = 0; i < FLUID_NFIELDS + 4; ++i)
             if (h->alloc_base[i] == h->scratch[alloc_id - FLUID_IPC_SCRATCH0] - FL_ZPAD * h->g.plane) slot = i;
     c->peer_alloc[peer_rank][slot] = (float*)p;
     return 0;

@@ -89,14 +89,61 @@ int fl_halo_exchange_on(fluid_handle* h, int n, float* const* fields, cudaStream
     return 0;
 }
 
-int fl_halo_exchange(fluid_handle* h, int n, float* const* fields) { return fl_halo_exchange_on(h, n, fields, h->stream); }
+// The exchange around divergence / gradient / advect.  With the neighbours' buffers mapped it is a hand-over like
+// the sweeps': one small kernel stores the FL_HALO boundary planes per side into the neighbours' halos and raises
+// their arrival flags, the stream then waits for its own two flags -- no rendezvous with NCCL's proxy on the
+// step's critical path.  One-sided stores are safe here because between any kernel that READS a halo and the
+// next hand-over INTO that halo every rank passes at least one other hand-over whose flag the writer waited for.
+int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stream, unsigned seq, int nplanes);
+int fl_halo_wait(fluid_handle* h, cudaStream_t stream, unsigned seq);
+bool fl_push_usable(fluid_handle* h);
+int fl_halo_exchange(fluid_handle* h, int n, float* const* fields)
+{
+    if (h->nranks == 1) return 0;
+    static const bool nccl_only = getenv("FLUID_XCHG_NCCL") != nullptr;   // A/B: ncclSend / ncclRecv as before
+    if (!nccl_only && fl_push_usable(h)) {
+        const unsigned seq = ++h->halo_seq;
+        if (int e = fl_halo_push(h, n, fields, h->stream, seq, FL_HALO)) return e;
+        return fl_halo_wait(h, h->stream, seq);
+    }
+    return fl_halo_exchange_on(h, n, fields, h->stream);
+}
 
-// all ranks' streams have reached this point before any continues (1-float all-reduce)
+struct BarrierArgs { unsigned* flag[8]; unsigned epoch; int nranks, rank; };
+// every earlier kernel of this stream is complete (stream order); fence, then tell every other rank
+__global__ void k_barrier_signal(const BarrierArgs a)
+{
+    __threadfence_system();
+    const int r = threadIdx.x;
+    if (r < a.nranks && r != a.rank && a.flag[r])
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.flag[r] + 32 + a.rank), "r"(a.epoch) : "memory");
+}
+
+// all ranks' streams have reached this point before any continues: epoch flags over NVLink where every
+// rank's flag block is mapped, else a 1-float all-reduce
+static inline bool fl_push_ready(fluid_handle* h);
 int fl_barrier(fluid_handle* h)
 {
     if (h->nranks == 1) return 0;
     SlabComm* c = (SlabComm*)h->comm;
-    if (!c || !c->comm) return fl_fail(h, FLUID_E_COMM, "barrier: no communicator attached");
+    if (!c) return fl_fail(h, FLUID_E_COMM, "barrier: no communicator attached");
+    static const bool nccl_only = getenv("FLUID_XCHG_NCCL") != nullptr;
+    bool all_mapped = !nccl_only && fl_push_ready(h);
+    for (int r = 0; r < h->nranks && all_mapped; ++r) if (r != h->rank && !c->peer_alloc[r][FLUID_IPC_SYNC]) all_mapped = false;
+    if (all_mapped) {
+        BarrierArgs a = {};
+        a.epoch = ++h->barrier_seq; a.nranks = h->nranks; a.rank = h->rank;
+        for (int r = 0; r < h->nranks; ++r) a.flag[r] = r == h->rank ? nullptr : (unsigned*)c->peer_alloc[r][FLUID_IPC_SYNC];
+        k_barrier_signal<<<1, 32, 0, h->stream>>>(a);
+        FL_CHECK_LAUNCH(h);
+        for (int r = 0; r < h->nranks; ++r) {
+            if (r == h->rank) continue;
+            CUresult e = c->WaitValue32((CUstream)h->stream, (CUdeviceptr)(h->d_sync + 32 + r), a.epoch, CU_STREAM_WAIT_VALUE_GEQ);
+            if (e != CUDA_SUCCESS) return fl_fail(h, FLUID_E_CUDA, "cuStreamWaitValue32 failed (%d)", (int)e);
+        }
+        return 0;
+    }
+    if (!c->comm) return fl_fail(h, FLUID_E_COMM, "barrier: no communicator attached");
     FL_NCCL(h, c, c->AllReduce(c->d_token, c->d_token, 1, ncclFloat, ncclSum, c->comm, h->stream));
     h->launches++;
     return 0;
@@ -108,7 +155,7 @@ static inline float* fl_peer_ptr(fluid_handle* h, int r, const float* local)
 {
     SlabComm* c = (SlabComm*)h->comm;
     if (!c) return nullptr;
-    for (int i = 0; i < FLUID_NFIELDS + 3; ++i)
+    for (int i = 0; i < FLUID_NFIELDS + 4; ++i)
         if (h->alloc_base[i] == local - FL_ZPAD * h->g.plane)
             return c->peer_alloc[r][i] ? c->peer_alloc[r][i] + FL_ZPAD * h->g.plane : nullptr;
     return nullptr;
@@ -148,10 +195,10 @@ static inline bool fl_push_ready(fluid_handle* h)
 }
 
 struct PushArgs {
-    const float4* src[6]; float4* dst[6];     // (field, side): two consecutive planes each
+    const float4* src[8]; float4* dst[8];     // (field, side): nplanes consecutive planes each
     unsigned* flag[2];                        // the neighbours' arrival flags for this rank (nullptr = no neighbour)
     unsigned* counter;
-    long long n4;                             // float4s per copy (2 planes)
+    long long n4;                             // float4s per copy
     int ncopy; unsigned seq;
 };
 
@@ -177,30 +224,31 @@ __global__ void __launch_bounds__(128) k_push_halo(const PushArgs a)
     }
 }
 
-// hand the halo planes of `fields` (the buffers a sweep just wrote) to the z-neighbours; seq = this
-// sweep's number in h->halo_seq order
-int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stream, unsigned seq)
+// hand the `nplanes` boundary planes per side of `fields` (the buffers a kernel just wrote) to the z-neighbours;
+// seq = this hand-over's number in h->halo_seq order
+int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stream, unsigned seq, int nplanes)
 {
     SlabComm* c = (SlabComm*)h->comm;
     const long long pl = h->g.plane;
+    if (n > 4) return fl_fail(h, FLUID_E_ARG, "halo push: %d fields", n);
     PushArgs a = {};
-    a.n4 = 2 * pl / 4; a.seq = seq; a.counter = h->d_sync + 4;
+    a.n4 = nplanes * pl / 4; a.seq = seq; a.counter = h->d_sync + 4;
     for (int side = 0; side < 2; ++side) {
         const int r = side == 0 ? h->rank - 1 : h->rank + 1;
         if (r < 0 || r >= h->nranks) continue;
         int zlo_r, dl_r; fl_slab_of(h->g.D, h->nranks, r, &zlo_r, &dl_r);
-        // my planes {1,2} -> lower neighbour's {Dl_r+1, Dl_r+2}; my {Dl-1,Dl} -> upper neighbour's {-1,0}.
+        // my planes 1 .. n -> lower neighbour's Dl_r+1 .. Dl_r+n; my Dl-n+1 .. Dl -> upper neighbour's 1-n .. 0.
         // The neighbour's flag [1] is "raised by its upper neighbour", [0] "by its lower neighbour".
         a.flag[side] = (unsigned*)c->peer_alloc[r][FLUID_IPC_SYNC] + (side == 0 ? 1 : 0);
         for (int i = 0; i < n; ++i) {
             float* peer = fl_peer_ptr(h, r, fields[i]);
             if (!peer) return fl_fail(h, FLUID_E_COMM, "halo push: buffer of rank %d is not IPC-mapped", r);
-            a.src[a.ncopy] = (const float4*)(fields[i] + (side == 0 ? 1 : (long long)(h->g.Dl - 1)) * pl);
-            a.dst[a.ncopy] = (float4*)(peer + (side == 0 ? (long long)(dl_r + 1) : -1LL) * pl);
+            a.src[a.ncopy] = (const float4*)(fields[i] + (side == 0 ? 1 : (long long)(h->g.Dl - nplanes + 1)) * pl);
+            a.dst[a.ncopy] = (float4*)(peer + (side == 0 ? (long long)(dl_r + 1) : (long long)(1 - nplanes)) * pl);
             ++a.ncopy;
         }
     }
-    const int ctas = 16;                                  // 128 threads, no shared memory: fits beside a resident sweep CTA
+    const int ctas = nplanes > 2 ? 64 : 16;               // 128 threads, no shared memory: fits beside a resident sweep CTA
     k_push_halo<<<ctas, 128, 0, stream>>>(a);
     FL_CHECK_LAUNCH(h);
     return 0;
@@ -208,12 +256,12 @@ int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stre
 
 // where the fused sweep kernel writes: per face (0 lower, 1 upper) the neighbour's mapping of `fields`,
 // its arrival flag for this rank and the neighbour-local index of the first halo plane
-int fl_push_targets(fluid_handle* h, int n, float* const* fields, float* (*peer)[3], unsigned** flag, int* zdst)
+int fl_push_targets(fluid_handle* h, int n, float* const* fields, float* (*peer)[4], unsigned** flag, int* zdst)
 {
     SlabComm* c = (SlabComm*)h->comm;
     for (int side = 0; side < 2; ++side) {
         flag[side] = nullptr; zdst[side] = 0;
-        for (int i = 0; i < 3; ++i) peer[side][i] = nullptr;
+        for (int i = 0; i < 4; ++i) peer[side][i] = nullptr;
         const int r = side == 0 ? h->rank - 1 : h->rank + 1;
         if (r < 0 || r >= h->nranks) continue;
         int zlo_r, dl_r; fl_slab_of(h->g.D, h->nranks, r, &zlo_r, &dl_r);

@@ -42,7 +42,7 @@ static int alloc_all(fluid_handle* h)
         h->alloc_base[i] = h->field[i];
         h->field[i] += FL_ZPAD * h->g.plane;
     }
-    for (int i = 0; i < 3; ++i) {
+    for (int i = 0; i < (h->nranks > 1 ? 4 : 3); ++i) {       // z-slabs: the fourth partner is IPC-mapped like the others
         FL_CUDA(h, cudaMalloc(&h->scratch[i], fbytes));
         FL_CUDA(h, cudaMemsetAsync(h->scratch[i], 0, fbytes, h->stream));
         h->alloc_base[FLUID_NFIELDS + i] = h->scratch[i];

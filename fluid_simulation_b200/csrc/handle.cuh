@@ -16,12 +16,13 @@ struct fluid_handle {
     cudaEvent_t ev_frame_packed = nullptr, ev_frame_done = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     float* field[FLUID_NFIELDS] = {};
-    float* scratch[4] = {};          // ping-pong partners of the batched solves ([3]: allocated on first use, one GPU only)
+    float* scratch[4] = {};          // ping-pong partners of the batched solves ([3]: z-slabs at creation, one GPU on first use)
     // Allocation starts (plane -1) in FLUID_IPC_* id order.  field[] / scratch[] are permuted by the
     // solver's pointer swaps, identically on every rank; a buffer's id is found by its address.
-    float* alloc_base[FLUID_NFIELDS + 3] = {};
+    float* alloc_base[FLUID_NFIELDS + 4] = {};
     unsigned* d_sync = nullptr;      // [0] / [1] = arrival flags raised by the lower / upper z-neighbour, [2] = CTA counter
-    unsigned halo_seq = 0;           // sweeps whose halos went out through peer stores so far
+    unsigned halo_seq = 0;           // halo hand-overs (sweeps, exchanges) that went out through peer stores so far
+    unsigned barrier_seq = 0;        // flag barriers so far (d_sync[32 + r] = epoch of rank r)
     unsigned char* cflags = nullptr; // per-cell flag bytes, same pitched geometry as the fields
     bool flags_dirty = true;
     unsigned long long flags_version = 0;   // bumped whenever the flag volume is rebuilt (derived tables follow it)

@@ -16,14 +16,15 @@ int fl_lex_solve(fluid_handle* h, int nb, const int* b, const int* fid, const in
 int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
                    float a, float c, bool* handled);                     // tiled.cuh
 bool fl_swap_instead_of_copy(fluid_handle* h);                            // sweep_stream.cuh
+bool fl_slab_batch4(fluid_handle* h);                                     // sweep_stream.cuh
 void fl_tiled_release(fluid_handle* h);                                  // tiled.cuh
 void fl_comm_release(fluid_handle* h);                                   // comm.cuh
 int fl_halo_exchange_on(fluid_handle* h, int n, float* const* fields, cudaStream_t stream);   // comm.cuh
 // comm.cuh: halo hand-over by peer stores + arrival flags (sweeps of the streaming kernel)
 bool fl_push_usable(fluid_handle* h);
-int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stream, unsigned seq);
+int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stream, unsigned seq, int nplanes = 2);
 int fl_halo_wait(fluid_handle* h, cudaStream_t stream, unsigned seq);
-int fl_push_targets(fluid_handle* h, int n, float* const* fields, float* (*peer)[3], unsigned** flag, int* zdst);
+int fl_push_targets(fluid_handle* h, int n, float* const* fields, float* (*peer)[4], unsigned** flag, int* zdst);
 int fl_barrier(fluid_handle* h);                                         // comm.cuh
 
 static inline int fl_rebuild_flags(fluid_handle* h)
@@ -270,7 +271,8 @@ static inline int fl_step_only(fluid_handle* h)
     // instead of per ~33).
     static const bool no_batch4 = getenv("FLUID_NO_BATCH4") != nullptr;
     const bool swap = fl_swap_instead_of_copy(h);
-    const bool batch4 = swap && !no_batch4 && !(h->flags & FLUID_ELIDE_DEAD);
+    // z-slabs batch the fourth field too (its ping-pong partner is IPC-mapped like the others); they keep the copies
+    const bool batch4 = (swap || fl_slab_batch4(h)) && !no_batch4 && !(h->flags & FLUID_ELIDE_DEAD);
     if (swap) {
         // :108-110 v_prev = v without moving bytes: the buffers trade places (v_prev now holds v, v a stale buffer
         // that the out-of-place solve below overwrites completely) and the solve's first sweep reads its initial

@@ -47,7 +47,7 @@ struct alignas(64) StreamArgs {
     int flip;                            // 1 = this sweep streams every segment against its planned direction
     // z-slabs, halos handed over inside the sweep (segments with a face in SwSeg.mode): the neighbour's
     // mapping of dst[] per face, its arrival flag for this rank, this rank's per-face CTA counters
-    float* peer_dst[2][3];
+    float* peer_dst[2][4];
     unsigned* peer_flag[2];
     unsigned* counter;
     int peer_zdst[2];                    // neighbour-local index of the first of the two halo planes written
@@ -873,7 +873,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     A.dbg = s->dbg;
 
     float* cur[4]; float* alt[4];
-    if (nb > 4 || (nb == 4 && h->nranks > 1)) return fl_fail(h, FLUID_E_ARG, "streaming solve: %d batched fields", nb);
+    if (nb > 4) return fl_fail(h, FLUID_E_ARG, "streaming solve: %d batched fields", nb);
     if (nb == 4 && !h->scratch[3]) {                                      // fourth ping-pong partner, first use
         const size_t fb = (size_t)g.cells * sizeof(float);
         FL_CUDA(h, cudaMalloc(&h->scratch[3], fb));
@@ -991,6 +991,15 @@ inline bool fl_swap_instead_of_copy(fluid_handle* h)
     if (off || h->nranks != 1 || h->acc <= 0 || !fl_tiled_eligible(h)) return false;
     StreamState* s = sw_state(h);
     return s->encode != nullptr && !s->unbatch;
+}
+
+// a z-slab runs the density diffusion (simulation.cpp:135) as the fourth field of the velocity diffusion when the
+// solve is certain to go through the streaming kernel with the peer-store hand-over (four mapped partners)
+bool fl_slab_batch4(fluid_handle* h)
+{
+    if (h->nranks == 1 || h->acc <= 0 || !fl_tiled_eligible(h) || !fl_push_usable(h)) return false;
+    StreamState* s = sw_state(h);
+    return s->encode != nullptr && !s->unbatch && h->scratch[3] != nullptr;
 }
 
 // linearSolver through the streaming kernel; *handled = false leaves the solve to the simple kernels

@@ -15,7 +15,8 @@ from .simulation import FIELDS, FluidError
 
 # the fields advect() gathers from: prev_field of each of the four calls (simulation.cpp:125-127, 136)
 GATHER_SOURCES = ("v_x_prev", "v_y_prev", "v_z_prev", "buffer")
-IPC_COUNT = len(FIELDS) + 4            # fields, 3 solver ping-pong partners, arrival-flag block (FLUID_IPC_COUNT)
+IPC_COUNT = len(FIELDS) + 5            # fields, 4 solver ping-pong partners, flag block (FLUID_IPC_COUNT)
+IPC_SYNC = len(FIELDS) + 4             # FLUID_IPC_SYNC: arrival flags of the z-neighbours, barrier epochs of every rank
 
 
 def nccl_library_path() -> str:
@@ -75,7 +76,7 @@ def attach(sim, dist, lib=None) -> None:
     for r, handles in enumerate(all_gather_bytes(dist, mine)):
         if r == rank:
             continue
-        wanted = range(IPC_COUNT) if abs(r - rank) == 1 else gather_ids
+        wanted = range(IPC_COUNT) if abs(r - rank) == 1 else gather_ids + [IPC_SYNC]
         for aid in wanted:
             sim._ck(L.fluid_ipc_import(sim._h, r, aid, handles[aid]))
     dist.barrier()

@@ -212,14 +212,16 @@ int fluid_comm_init(fluid_handle*, const char* nccl_lib_path, const char unique_
  * the host program) and read over NVLink by the advection kernel.
  * The linearSolver sweeps (simulation.cpp:258-272) hand their halo planes to the z-neighbours the same
  * way once the neighbours' allocations are mapped: ids 0..FLUID_NFIELDS-1 are the fields,
- * FLUID_IPC_SCRATCH0..+2 the solver's ping-pong partners and FLUID_IPC_SYNC the arrival flags.  With all
+ * FLUID_IPC_SCRATCH0..+3 the solver's ping-pong partners and FLUID_IPC_SYNC the flag block (arrival flags
+ * of the two z-neighbours, barrier epochs of every rank: import it from ALL ranks).  With all
  * of them imported from both neighbours a sweep ends in one small kernel that stores the two boundary
  * planes straight into the neighbour's halo and raises its flag (the neighbour's streams wait on the
  * flag with a stream memory operation); otherwise the exchange after a sweep is an ncclSend/ncclRecv. */
-enum { FLUID_IPC_SCRATCH0 = FLUID_NFIELDS, FLUID_IPC_SYNC = FLUID_NFIELDS + 3, FLUID_IPC_COUNT = FLUID_NFIELDS + 4 };
+enum { FLUID_IPC_SCRATCH0 = FLUID_NFIELDS, FLUID_IPC_SYNC = FLUID_NFIELDS + 4, FLUID_IPC_COUNT = FLUID_NFIELDS + 5 };
 int fluid_ipc_export(fluid_handle*, int alloc_id, char out[64]);
 int fluid_ipc_import(fluid_handle*, int peer_rank, int alloc_id, const char in[64]);
-/* device-side barrier across all ranks on the handle's stream (collective) */
+/* device-side barrier across all ranks on the handle's stream (collective): epoch flags stored into every
+ * rank's flag block over NVLink where those are mapped, a one-float ncclAllReduce otherwise */
 int fluid_barrier(fluid_handle*);
 
 #ifdef __cplusplus
