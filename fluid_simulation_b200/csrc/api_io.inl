@@ -120,14 +120,49 @@ int fluid_streamlines(fluid_handle* h, const fluid_streamline_params* params, in
     return fl_streamlines(h, params, max_lines, max_points, n_lines, n_points, line_len, norm_speed, points);
 }
 
+// Batched mutators keep the reference's per-call semantics when a cell appears more than once in a batch
+// (simulation.cpp:155-178 runs the calls one after the other): occurrence[i] = how many earlier entries name the
+// same cell.  A batch in strictly increasing cell order (the usual loop nest) has none and skips the hashing.
+static int occurrences(const fluid_handle* h, int n, const int* xyz, std::vector<int>* occ)
+{
+    const long long Wp = h->g.W + 2, Hp = h->g.H + 2;
+    auto lin = [&](int i) { return xyz[3 * i] + Wp * (xyz[3 * i + 1] + Hp * (long long)xyz[3 * i + 2]); };
+    bool increasing = true;
+    for (int i = 1; i < n && increasing; ++i) increasing = lin(i) > lin(i - 1);
+    if (increasing) return 0;
+    std::unordered_map<long long, int> seen;
+    seen.reserve((size_t)n * 2);
+    occ->assign((size_t)n, 0);
+    int most = 0;
+    for (int i = 0; i < n; ++i) { const int k = seen[lin(i)]++; (*occ)[i] = k; if (k > most) most = k; }
+    return most;
+}
+
 int fluid_add_density(fluid_handle* h, int n, const int* xyz, const float* amount)
 {
     if (int e = check_xyz(h, n, xyz, "fluid_add_density")) return e;
     if (n == 0) return 0;
     if (!amount) return fl_fail(h, FLUID_E_ARG, "fluid_add_density: null amounts");
-    if (int e = sparse_stage(h, n, xyz, amount, 1)) return e;
-    k_add_density<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_DENS], n, h->d_xyz, h->d_val);
-    FL_CHECK_LAUNCH(h);
+    std::vector<int> occ;
+    const int most = occurrences(h, n, xyz, &occ);
+    if (most == 0) {
+        if (int e = sparse_stage(h, n, xyz, amount, 1)) return e;
+        k_add_density<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_DENS], n, h->d_xyz, h->d_val);
+        FL_CHECK_LAUNCH(h);
+        return 0;
+    }
+    // repeated cells: round k adds the k-th mention of every cell, so each cell's float additions happen in call
+    // order (one addition per cell and launch: the atomicAdd is then an ordinary, deterministic addition)
+    std::vector<int> xs; std::vector<float> am;
+    for (int k = 0; k <= most; ++k) {
+        xs.clear(); am.clear();
+        for (int i = 0; i < n; ++i) if (occ[i] == k) { xs.insert(xs.end(), xyz + 3 * i, xyz + 3 * i + 3); am.push_back(amount[i]); }
+        const int m = (int)am.size();
+        if (int e = sparse_stage(h, m, xs.data(), am.data(), 1)) return e;
+        k_add_density<<<(m + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_DENS], m, h->d_xyz, h->d_val);
+        FL_CHECK_LAUNCH(h);
+        FL_CUDA(h, cudaStreamSynchronize(h->stream));       // the host staging vectors are reused by the next round
+    }
     return 0;
 }
 
@@ -136,6 +171,25 @@ int fluid_set_velocity(fluid_handle* h, int n, const int* xyz, const float* v)
     if (int e = check_xyz(h, n, xyz, "fluid_set_velocity")) return e;
     if (n == 0) return 0;
     if (!v) return fl_fail(h, FLUID_E_ARG, "fluid_set_velocity: null values");
+    std::vector<int> occ;
+    if (occurrences(h, n, xyz, &occ) > 0) {
+        // repeated cells: the last call wins (simulation.cpp:172-177), so only each cell's last mention is staged
+        std::vector<int> last((size_t)n, 0), xs; std::vector<float> vs;
+        {
+            const long long Wp = h->g.W + 2, Hp = h->g.H + 2;
+            std::unordered_map<long long, int> at;
+            for (int i = 0; i < n; ++i) at[xyz[3 * i] + Wp * (xyz[3 * i + 1] + Hp * (long long)xyz[3 * i + 2])] = i;
+            for (auto& kv : at) last[(size_t)kv.second] = 1;
+        }
+        for (int i = 0; i < n; ++i) if (last[i]) { xs.insert(xs.end(), xyz + 3 * i, xyz + 3 * i + 3); vs.insert(vs.end(), v + 3 * i, v + 3 * i + 3); }
+        const int m = (int)xs.size() / 3;
+        if (int e = sparse_stage(h, m, xs.data(), vs.data(), 3)) return e;
+        k_set_velocity<<<(m + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY],
+                                                              h->field[FLUID_VZ], m, h->d_xyz, h->d_val);
+        FL_CHECK_LAUNCH(h);
+        FL_CUDA(h, cudaStreamSynchronize(h->stream));       // the host staging vectors go out of scope
+        return 0;
+    }
     if (int e = sparse_stage(h, n, xyz, v, 3)) return e;
     k_set_velocity<<<(n + 255) / 256, 256, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY],
                                                           h->field[FLUID_VZ], n, h->d_xyz, h->d_val);

@@ -11,6 +11,7 @@
 #include "postproc.cuh"
 #include <cstring>
 #include <new>
+#include <unordered_map>
 
 thread_local std::string g_fluid_create_error;
 

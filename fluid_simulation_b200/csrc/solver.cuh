@@ -136,7 +136,13 @@ static inline int fl_lin_solve_impl(fluid_handle* h, int nb, const int* b, const
                 FL_CHECK_LAUNCH(h);
             }
         }
-        if (h->nranks > 1) if (int e = fl_halo_exchange(h, nb, cur)) return e;
+        // The in-place red-black kernels read (and, for colour 0, write) the very halo planes the neighbour's next
+        // hand-over lands in, with no other hand-over in between: a one-sided peer store could arrive while they still
+        // run.  This path keeps the two-sided NCCL exchange; the ping-pong Jacobi form may hand over by peer stores.
+        if (h->nranks > 1) {
+            if (solver == FLUID_SOLVER_JACOBI) { if (int e = fl_halo_exchange(h, nb, cur)) return e; }
+            else                               { if (int e = fl_halo_exchange_on(h, nb, cur, h->stream)) return e; }
+        }
     }
     // Jacobi ping-pong: the result may live in the scratch buffer -> swap ownership, no copy
     for (int i = 0; i < nb; ++i) {

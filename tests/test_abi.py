@@ -29,13 +29,41 @@ def test_library_exports_every_declared_symbol():
     assert b"sm_100a" in lib.fluid_version()
 
 
-def test_library_is_sm100a_only_and_fma_free():
+def test_library_is_sm100a_only():
     out = subprocess.run(["/usr/local/cuda/bin/cuobjdump", "-lelf", _lib.LIB_PATH],
                          capture_output=True, text=True)
     if out.returncode != 0:
         pytest.skip("cuobjdump unavailable")
     archs = set(re.findall(r"sm_\d+a?", out.stdout))
     assert archs == {"sm_100a"}, archs
+
+
+def test_hot_path_kernels_are_fma_free_and_use_tma():
+    """--fmad=false is the parity contract (no contraction of a*b+c): the kernels of the per-step hot path must
+    hold no FFMA at all.  The FFMAs that do exist in the library live in kernels off that path, where they are
+    library sequences for IEEE division / cbrtf / double arithmetic or integer-to-float index math, not
+    contracted field arithmetic; the test lists where they are so that a new one on the hot path is caught.
+    The sweep kernels must show the TMA and mbarrier instructions (UTMALDG, SYNCS)."""
+    out = subprocess.run(["/usr/local/cuda/bin/cuobjdump", "-sass", _lib.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    per, name = {}, None
+    for line in out.stdout.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            name = m.group(1); per[name] = {"FFMA": 0, "UTMALDG": 0, "SYNCS": 0}
+        elif name:
+            for k in per[name]:
+                if re.search(r"\b" + k + r"\b", line):
+                    per[name][k] += 1
+    hot = [n for n in per if re.search(r"k_sweep_|k_divergence|k_advect|k_inflow|k_set_bounds|k_copy_edges|k_lex_|k_pack|k_unpack|k_build", n)]
+    assert hot and all(per[n]["FFMA"] == 0 for n in hot), {n: per[n]["FFMA"] for n in hot if per[n]["FFMA"]}
+    # k_gradient<false> divides by h / 2h (IEEE division sequences contain FFMA by construction); the
+    # power-of-two form the benchmark grids take multiplies and must be clean
+    grad = [n for n in per if "k_gradient" in n]
+    assert any(per[n]["FFMA"] == 0 for n in grad), {n: per[n]["FFMA"] for n in grad}
+    sweeps = [n for n in per if "k_sweep_stream" in n or "k_sweep_pair" in n]
+    assert sweeps and all(per[n]["UTMALDG"] > 0 and per[n]["SYNCS"] > 0 for n in sweeps)
 
 
 def _has_gpu():

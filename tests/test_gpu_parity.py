@@ -183,3 +183,21 @@ def test_invariants_large_grid():
     dens = sim.get("dens")
     assert np.all(dens[1:-1, 0, 1:-1] == dens[1:-1, 1, 1:-1])
     assert dens.max() > 0
+
+
+def test_batched_mutators_with_repeated_cells():
+    """A batch that names a cell more than once behaves like the reference's sequence of calls
+    (simulation.cpp:155-178): densities add up in call order (float rounding included), the last
+    setVelocity wins."""
+    gpu, cpu = make_pair(12, 10, 8, 3, 0, ORDER_RB)
+    rng = np.random.default_rng(9)
+    cells = np.array([[2, 3, 4], [5, 5, 5], [2, 3, 4], [7, 1, 2], [2, 3, 4], [5, 5, 5]], dtype=np.int32)
+    amounts = np.array([1e-8, 0.3, 0.7, 0.25, 1e8, -0.3], dtype=np.float32)          # order-sensitive in float32
+    vel = rng.uniform(-1, 1, (len(cells), 3)).astype(np.float32)
+    gpu.add_density_cells(np.ascontiguousarray(cells), amounts)
+    gpu.set_velocity_cells(np.ascontiguousarray(cells), np.ascontiguousarray(vel))
+    for (x, y, z), a in zip(cells, amounts):
+        cpu.add_density(int(x), int(y), int(z), float(a))
+    for (x, y, z), v in zip(cells, vel):
+        cpu.set_velocity(int(x), int(y), int(z), float(v[0]), float(v[1]), float(v[2]))
+    check(gpu, cpu, "repeated cells in one batch")

@@ -41,6 +41,38 @@ def test_frame_is_a_complete_state_oracle():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("w,h,d", [(64, 16, 8), (128, 16, 8)])
+def test_restart_on_the_streaming_path(tmp_path, w, h, d):
+    """W >= 64: the default production path (TMA streaming sweeps, v <-> v_prev buffer swap with the first sweep
+    reading its guess from the right-hand side, the 4-field diffusion launch with its lazily allocated fourth
+    partner).  A restart begins from zeroed scratch / prev buffers while the uninterrupted run has stale,
+    permuted ones; the frames must not depend on that.  The restart frame carries NON-ZERO edge and corner
+    ghosts (the reference never writes them, so they persist), which pins the edge-copy path."""
+    from fluid_simulation_b200 import Simulation
+    rng = np.random.default_rng(4)
+    a = Simulation(w, h, d, 5, acc=5)
+    a.set("obs", masks.box(w, h, d))
+    for f in ("dens", "v_x", "v_y", "v_z"):                     # edges / corners of the padded volume
+        v = np.zeros(a.shape, np.float32)
+        e = rng.uniform(0.5, 1.5, a.shape).astype(np.float32)
+        edge = np.zeros(a.shape, bool)
+        edge[0, 0, :] = edge[0, -1, :] = edge[-1, 0, :] = edge[-1, -1, :] = True
+        edge[0, :, 0] = edge[0, :, -1] = edge[-1, :, 0] = edge[-1, :, -1] = True
+        edge[:, 0, 0] = edge[:, 0, -1] = edge[:, -1, 0] = edge[:, -1, -1] = True
+        v[edge] = e[edge]
+        a.set(f, v)
+    a.run(str(tmp_path / "a"), verbose=False)
+    b = Simulation(w, h, d, 2, acc=5)
+    assert b.restart_from_frames(str(tmp_path / "a"), 2) == 2
+    b.run(str(tmp_path / "b"), verbose=False)
+    for name in ("data.bin", "obs.bin", "v_x.bin", "v_y.bin", "v_z.bin"):
+        full = np.fromfile(tmp_path / "a" / name, dtype=np.float32).reshape(5, -1)
+        tail = np.fromfile(tmp_path / "b" / name, dtype=np.float32).reshape(2, -1)
+        assert np.array_equal(full[3:].view(np.uint32), tail.view(np.uint32)), name
+    assert np.any(np.fromfile(tmp_path / "b" / "v_x.bin", dtype=np.float32).reshape(2, *a.shape)[1, 0, 0, :] != 0)
+
+
+@pytest.mark.gpu
 def test_python_restart_and_sidecar(tmp_path):
     from fluid_simulation_b200 import Simulation, FluidError
     w, h, d = 40, 24, 20
@@ -74,7 +106,7 @@ def test_cpp_restart(tmp_path):
     if not os.path.exists(exe):
         pytest.skip("fluid_tunnel not built")
     (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
-    common = [exe, "--w", "36", "--h", "20", "--d", "16", "--acc", "4", "--quiet"]
+    common = [exe, "--w", "72", "--h", "20", "--d", "16", "--acc", "4", "--quiet"]        # W >= 64: streaming path
     r = subprocess.run(common + ["--iter", "4", "--obstacle", "sphere", "--out", str(tmp_path / "a")], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr
     r = subprocess.run(common + ["--iter", "3", "--restart", f"{tmp_path / 'a'}:0", "--out", str(tmp_path / "b")], capture_output=True, text=True, timeout=300)
@@ -84,6 +116,6 @@ def test_cpp_restart(tmp_path):
         tail = np.fromfile(tmp_path / "b" / name, dtype=np.uint32).reshape(3, -1)
         assert np.array_equal(full[1:], tail), name
     meta = json.load(open(tmp_path / "b" / "meta.json"))
-    assert meta["frames"] == 3 and meta["width"] == 36
+    assert meta["frames"] == 3 and meta["width"] == 72
     r = subprocess.run(common + ["--iter", "1", "--restart", f"{tmp_path / 'a'}:9", "--out", str(tmp_path / "b")], capture_output=True, text=True, timeout=300)
     assert r.returncode != 0 and "frame out of range" in r.stderr
