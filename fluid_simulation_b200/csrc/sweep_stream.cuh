@@ -44,6 +44,8 @@ struct alignas(64) StreamArgs {
     Grid g;
     float a, c_recip;
     int nty;                             // row tiles per field
+    int nxt, xt_cells;                   // x tiles per row tile and the cells each owns (W > 128 * TXW: a CTA spans part of x,
+                                         // one redundantly computed halo quad beside every interior tile edge); 1, W otherwise
     int flip;                            // 1 = this sweep streams every segment against its planned direction
     // z-slabs, halos handed over inside the sweep (segments with a face in SwSeg.mode): the neighbour's
     // mapping of dst[] per face, its arrival flag for this rank, this rank's per-face CTA counters
@@ -333,19 +335,21 @@ __device__ __forceinline__ void sw_await_face(const StreamArgs& A, int side, int
 // Nothing waits for the stores here; sw_signal_face fences them when the segment is done.
 template <int TY, int THREADS>
 __device__ __forceinline__ void sw_push_face(const StreamArgs& A, const Grid& g, const float* out, int batch, int tile,
-                                             int y0, int side, int tid)
+                                             int y0, int q_lo, int q_hi, int side, int tid)
 {
     // (the __syncthreads that ended the previous step made the CTA's stores visible to the CTA)
+    // rows r0 .. r1, float4 columns q_lo .. q_hi-1 of each row: the cells this column's CTA wrote (an x tile
+    // takes only its own part of a row; the first / last tile also the x ghosts and the row padding)
     const int r0 = tile == 0 ? 0 : y0;
     const int r1 = tile == A.nty - 1 ? g.rows - 1 : y0 + TY - 1;
-    const int n4 = (r1 - r0 + 1) * (g.pitch / 4);
+    const int nq = q_hi - q_lo, n4 = (r1 - r0 + 1) * nq, p4 = g.pitch / 4;
     const long long zsrc = side == 0 ? 1 : g.Dl - 1;
 #pragma unroll
     for (int pl = 0; pl < 2; ++pl) {
         const float4* __restrict__ s4 = reinterpret_cast<const float4*>(out + (zsrc + pl) * g.plane + (long long)r0 * g.pitch);
         float4* __restrict__ d4 = reinterpret_cast<float4*>(A.peer_dst[side][batch] + ((long long)A.peer_zdst[side] + pl) * g.plane +
                                                             (long long)r0 * g.pitch);
-        for (int i = tid; i < n4; i += THREADS) d4[i] = __ldcg(s4 + i);
+        for (int i = tid; i < n4; i += THREADS) { const int r = i / nq, q = q_lo + (i - r * nq); d4[r * p4 + q] = __ldcg(s4 + r * p4 + q); }
     }
 }
 
@@ -370,8 +374,8 @@ __device__ __forceinline__ void sw_signal_face(const StreamArgs& A, int side, in
 template <int TXW, int NP, int CPS, int MODE, int DIR>
 __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, SwThread& t, float* const uring,
                                            float* const vbuf, unsigned long long* const bars, int& s_iss, int& s_con,
-                                           unsigned& ph_con, const int tid, const int pr, const int rA, const int x0,
-                                           const bool lane_in, const unsigned exbits, const unsigned safe)
+                                           unsigned& ph_con, const int tid, const int pr, const int rA, const int qx,
+                                           const unsigned safe)
 {
     using GE = SwGeom<TXW, NP, CPS>;
     constexpr int BOXF = GE::BOXF, RBOXF = GE::RBOXF, SLOTF = GE::SLOTF, XSLOTF = GE::XSLOTF;
@@ -380,8 +384,17 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     const unsigned plane = (unsigned)g.plane;
     const unsigned dplane = DIR > 0 ? plane : 0u - plane;
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    const int batch = sg.col / A.nty;
-    const int y0 = 1 + (sg.col - batch * A.nty) * GE::TY;        // first owned row (odd)
+    // column = ((batched field * x tiles) + x tile) * row tiles + row tile
+    const int bx = sg.col / A.nty;
+    const int batch = bx / A.nxt, xtile = bx - batch * A.nxt;
+    const int y0 = 1 + (sg.col - bx * A.nty) * GE::TY;           // first owned row (odd)
+    const int own_lo = 1 + xtile * A.xt_cells;                   // first cell the tile owns
+    const int own_hi = min(own_lo + A.xt_cells - 1, g.W);
+    const int xo = own_lo - 1 - (xtile > 0 ? 4 : 0);             // x offset of the CTA's first quad (a halo quad inside the grid)
+    const int x0 = 1 + xo + 4 * qx;                              // this thread's quad: cells x0 .. x0+3
+    const bool lane_in = x0 <= g.W;
+    const bool own_x = x0 >= own_lo && x0 <= own_hi;
+    const unsigned exbits = (x0 == 1 ? SW_XLO : 0u) | (x0 + 3 == g.W ? SW_XHI : 0u);
     const int za = sg.za, zb = sg.zb;
     const int lo = max(za - 2, g.zl_lo), hi = min(zb + 2, g.zl_hi);   // planes this segment reads
     const int ps = DIR > 0 ? za - 1 : zb + 1;                    // first stage-0 plane
@@ -403,8 +416,8 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
 #pragma unroll
             for (int i = 0; i < TXW; ++i) {
                 // the tensor maps start at the allocation's first plane, -FL_ZPAD
-                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], 128 * i, y0 - 2, p + FL_ZPAD, bar);
-                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + 128 * i, y0 - 1, p + FL_ZPAD, bar);
+                sw_tma_load_3d(slot + i * BOXF, &A.map[batch], xo + 128 * i, y0 - 2, p + FL_ZPAD, bar);
+                sw_tma_load_3d(slot + XSLOTF + i * RBOXF, &A.rmap[batch], FL_XOFF + 1 + xo + 128 * i, y0 - 1, p + FL_ZPAD, bar);
             }
         }
         if (++s_iss == NSLOT) s_iss = 0;
@@ -416,8 +429,8 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     const int yA = y0 - 2 + rA, yB = yA + 1;
     t.intA = lane_in && yA >= 1 && yA <= g.H;                    // row takes part in stage 0
     t.intB = lane_in && yB >= 1 && yB <= g.H;
-    t.ownA = t.intA && pr >= 1;                                  // row is stored by this CTA
-    t.ownB = t.intB && pr <= NP - 2;
+    t.ownA = t.intA && pr >= 1 && own_x;                         // quad is stored by this CTA
+    t.ownB = t.intB && pr <= NP - 2 && own_x;
     t.eA = exbits | (yA == 1 ? SW_YLO : 0u) | (yA == g.H ? SW_YHI : 0u);
     t.eB = exbits | (yB == 1 ? SW_YLO : 0u) | (yB == g.H ? SW_YHI : 0u);
     // element offsets (32-bit: the padded volume has < 2^32 cells).  Rows / lanes outside the
@@ -471,7 +484,7 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     // A face segment streams away from its slab face: after four steps the two boundary planes are final
     // and go to the z-neighbour while the rest of the segment is still being swept.
     const int face = (sg.mode >> 1) - 1;
-#define SW_HAND_OVER if (face >= 0 && step == 4 && !(A.dbg & 8)) sw_push_face<GE::TY, GE::THREADS>(A, g, out, batch, sg.col - batch * A.nty, y0, face, tid);
+#define SW_HAND_OVER if (face >= 0 && step == 4 && !(A.dbg & 8)) sw_push_face<GE::TY, GE::THREADS>(A, g, out, batch, sg.col - bx * A.nty, y0, xtile == 0 ? 0 : (FL_XOFF + own_lo) / 4, xtile == A.nxt - 1 ? g.pitch / 4 : (FL_XOFF + own_hi + 1) / 4, face, tid);
     if (((g.zlo + ps) & 1) == 0) { for (;;) { SW_HAND_OVER SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
     else                         { for (;;) { SW_HAND_OVER SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
 #undef SW_STEP
@@ -514,15 +527,13 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
     // what is constant for the thread across segments
     SwThread t;
     t.lane = lane; t.sink = 0;
-    const int x0 = 1 + 4 * (32 * wx + lane);
+    const int qx = 32 * wx + lane;                                   // this thread's quad within the CTA's x extent
     const int rA = 1 + 2 * pr;
-    const bool lane_in = x0 <= g.W;
     t.offA = wx * BOXF + rA * SW_BOXW + 4 * (lane + 1); t.offB = t.offA + SW_BOXW;
     t.roffA = XSLOTF + wx * RBOXF + (rA - 1) * SW_RBOXW + 4 * lane; t.roffB = t.roffA + SW_RBOXW;
     // warp-edge lanes publish their outer cell into the neighbour column's halo, or copy the x ghosts
     t.pub_gl = lane == 0 && wx == 0;        t.pub_nl = lane == 0 && wx > 0;
     t.pub_gr = lane == 31 && wx == TXW - 1; t.pub_nr = lane == 31 && wx + 1 < TXW;
-    const unsigned exbits = (x0 == 1 ? SW_XLO : 0u) | (x0 + 3 == g.W ? SW_XHI : 0u);
     const unsigned safe = (unsigned)fl_idx(g, 1, 1, 0);
 
     int s_iss = 0;                                                   // ring slot the next TMA plane goes to
@@ -535,9 +546,9 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
         const bool down = DIRS == 0 ? false : DIRS == 1 ? true
                         : (sg.mode >> 1) ? (sg.mode >> 1) == 2 : (((sg.mode ^ A.flip) & 1) != 0);
         if (down)
-            sw_segment<TXW, NP, CPS, MODE, -1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, x0, lane_in, exbits, safe);
+            sw_segment<TXW, NP, CPS, MODE, -1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, qx, safe);
         else
-            sw_segment<TXW, NP, CPS, MODE, 1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, x0, lane_in, exbits, safe);
+            sw_segment<TXW, NP, CPS, MODE, 1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, qx, safe);
     }
     if (A.nty < 0) A.dst[0][0] = __uint_as_float(t.sink);            // never taken: keeps t.sink observable
 }
@@ -861,14 +872,22 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     const bool overlap = h->nranks > 1 && s->overlap && s->zc_override == 0 && g.Dl >= 4 * s->edge;
     const bool push = h->nranks > 1 && fl_push_usable(h);
     const bool fused = overlap && push;
+    // x tiles: a grid wider than the CTA's 128 * TXW cells is cut into tiles of equal width, each with one halo
+    // quad beside every interior edge (x is read 1 + 2/62 times instead of once; the alternative -- a CTA as wide as
+    // the grid with two owned rows -- read it three times).  The plan sees (field, x tile) pairs as its "fields".
+    const int nq = g.W / 4, qmax = 32 * TXW;
+    int nxt = 1, xq = nq;
+    if (nq > qmax) { nxt = (nq - 2 + (qmax - 2) - 1) / (qmax - 2); xq = (nq + nxt - 1) / nxt; }
+    const int nbx = nb * nxt;
     SwPlan plan, plan_edge;
-    if (int e = sw_get_plan(h, nb, GE::TY, CPS, fused ? (s->face_cta ? 4 : 5) : overlap ? 2 : 0, &plan)) return e;
-    if (overlap && !fused) if (int e = sw_get_plan(h, nb, GE::TY, CPS, 1, &plan_edge)) return e;
+    if (int e = sw_get_plan(h, nbx, GE::TY, CPS, fused ? (s->face_cta ? 4 : 5) : overlap ? 2 : 0, &plan)) return e;
+    if (overlap && !fused) if (int e = sw_get_plan(h, nbx, GE::TY, CPS, 1, &plan_edge)) return e;
     StreamArgs A;
     A.g = g; A.a = a; A.c_recip = 1.0f / c;                              // simulation.cpp:257
     if (int e = sw_get_zbits(h)) return e;
     A.zbits[0] = s->zbits[0]; A.zbits[1] = s->zbits[1]; A.zb_lanes = s->zb_lanes; A.zb_plane = (unsigned)(s->zb_pairs * s->zb_lanes);
     A.nty = (g.H + GE::TY - 1) / GE::TY;
+    A.nxt = nxt; A.xt_cells = 4 * xq;
     A.segs = plan.segs; A.seg_first = plan.seg_first;
     A.dbg = s->dbg;
 
@@ -923,7 +942,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         const unsigned seq = push ? ++h->halo_seq : 0u;
         if (fused) {
             if (int e = fl_push_targets(h, nb, alt, A.peer_dst, A.peer_flag, A.peer_zdst)) return e;
-            A.counter = h->d_sync + 2; A.n_edge = nb * A.nty; A.seq = seq;
+            A.counter = h->d_sync + 2; A.n_edge = nbx * A.nty; A.seq = seq;
             A.my_flag = h->d_sync; A.err_word = h->d_sync + 16;
         } else if (overlap) {
             // ev_a = "the in-between planes of the previous sweep (or whatever preceded the solve) are done"
@@ -978,7 +997,7 @@ inline bool fl_tiled_eligible(fluid_handle* h)
     const unsigned solver = h->flags & FLUID_SOLVER_MASK;
     if (h->flags & FLUID_NO_TILED) return false;
     if (solver != FLUID_SOLVER_RB && solver != FLUID_SOLVER_JACOBI) return false;
-    if ((g.W & 3) || g.W > 1024) return false;            // quads must not straddle the x = W+1 ghost
+    if ((g.W & 3) || g.W > 8192) return false;            // quads must not straddle the x = W+1 ghost
     if (!(h->flags & FLUID_TILED_ALWAYS) && (g.W < 64 || g.H < 8 || g.Dl < 4)) return false;
     return true;
 }
@@ -1027,14 +1046,16 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
         if (!jac && per <= 4) { e = fl_pair_solve(h, per, bb, ff, pp, a, c, xfr, &done); if (e) return e; if (done) xfr = 0u; }
         const int rest = h->acc - done;
         if (rest <= 0) continue;
+        // W <= 128: one warp column, 30 owned rows; <= 256: two, 14 rows; <= 512: four, 6 rows; wider grids: the
+        // two-column CTA in x tiles (measured at 1024 x 512 x 64: 112 us per field-sweep, 0.55 of the roofline, against
+        // 194 us / 0.32 for round 1's eight-column CTA with two owned rows; at W = 512 the tiles fill only 45 of 64
+        // lanes and lose to the four-column CTA, 0.54 against 0.69 -- FLUID_SW_CFG=5 forces them there for A/B)
         if (g.W <= 128)      e = sw_run<1, 16, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
-        else if (g.W <= 256) {
-            if (s->cfg == 1)      e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
-            else if (s->cfg == 2) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
-            else if (s->cfg == 3) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
-            else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
-        } else if (g.W <= 512) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
-        else                   e = sw_run<8, 2, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);   // two owned rows: x re-read twice
+        else if (s->cfg == 1 && g.W <= 256) e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+        else if (s->cfg == 2 && g.W <= 256) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+        else if (s->cfg == 3 && g.W <= 256) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+        else if (g.W > 256 && g.W <= 512 && s->cfg != 5) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+        else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         if (e) return e;
     }
     *handled = true;
