@@ -449,6 +449,10 @@ def run_e2e(sim, args, w, h, d, mask, barrier, reduce_max, rank, world):
     # buffers (cudaHostAlloc of 4 x 69 MB takes longer than a whole step) and the device staging
     sim.dump_frame_async(); sim.frame_wait()
     barrier()
+    td = time.perf_counter()                              # one frame dump alone, every rank at once: the host link's
+    sim.dump_frame_async(); sim.frame_wait()              # share of a step when the dumps do not hide behind compute
+    dump_alone = reduce_max(time.perf_counter() - td)
+    barrier()
     t0 = time.perf_counter()
     sim.set("obs", mask)                                  # obstacle mask H2D (once, amortised)
     for _ in range(steps):
@@ -464,6 +468,7 @@ def run_e2e(sim, args, w, h, d, mask, barrier, reduce_max, rank, world):
     h2d = (xyz_p.nbytes + amt_p.nbytes) * world + mask.nbytes // steps   # whole job
     return {"value": w * h * d * steps / dt / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": dt * 1e3 / steps,
+            "frame_dump_alone_ms": dump_alone * 1e3, "frame_dump_alone_gbs_per_gpu": d2h / world / dump_alone / 1e9,
             "path": "fluid_add_density(H2D) + buffer=dens + step() + fluid_dump_frame_async(D2H, pinned)"}
 
 

@@ -22,6 +22,7 @@ SYMBOLS = {
     "fluid_create_slab": (_p, [_i, _i, _i, _i, _f, _f, _f, _i, _u, _i, _i]),
     "fluid_destroy": (None, [_p]),
     "fluid_set_acc": (_i, [_p, _i]),
+    "fluid_set_params": (_i, [_p, _i, _f, _f, _f, _i]),
     "fluid_get_dims": (_i, [_p, _ip, _ip, _ip, _ip, _ip]),
     "fluid_upload_field": (_i, [_p, _i, _p]),
     "fluid_download_field": (_i, [_p, _i, _p]),

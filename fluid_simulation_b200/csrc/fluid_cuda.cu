@@ -182,6 +182,13 @@ int fluid_set_acc(fluid_handle* h, int acc)
     return 0;
 }
 
+int fluid_set_params(fluid_handle* h, int speed, float dt, float diff, float visc, int acc)
+{
+    if (!h || acc < 0) return fl_fail(h, FLUID_E_ARG, "fluid_set_params: bad argument");
+    h->speed = speed; h->dt = dt; h->diff = diff; h->visc = visc; h->acc = acc;
+    return 0;
+}
+
 int fluid_get_dims(fluid_handle* h, int* w, int* hh, int* d, int* z_lo, int* d_local)
 {
     if (!h) return FLUID_E_ARG;

@@ -3,14 +3,17 @@
 // reference's format and prints run()'s statistics plus the device time per step.
 //   fluid_tunnel [--w 128 --h 64 --d 64 --iter 100 --acc 15 --speed 30] [--obstacle none|sphere|box|FILE.bin|FILE.stl]
 //                [--restart DIR[:FRAME]] [--stl-scale 0.8 --stl-rot rx,ry,rz --stl-translate tx,ty,tz --stl-sampling hashed|fixed|cells]
-//                [--solver rb|jacobi|lex] [--elide] [--out data] [--dump-every 1] [--quiet]
+//                [--solver rb|jacobi|lex] [--elide] [--out data] [--dump-every 1] [--quiet] [--gpus N]
 //                [--view-ppm FILE [--view-field dens|v_x|v_y|v_z] [--view-z N]] [--view-streamlines FILE]
 // --view-*: after the run, what the reference's viewers would draw from the last frame (gui.py:265-300 z-slice as a
 // binary PPM; GUI/utils.py:118-214 streamlines as text: "line <n> <norm_speed>" followed by n "x y z" rows, origin
 // shifted by -1 as GUI/main_window.py:236 does), computed on the device.
+// --gpus N (N > 1): z-slabs on N GPUs of this node -- one forked process per GPU (slab_hub.h), halos handed over between
+// the GPUs inside libfluid_cuda, frames written by every rank into the same files; the output equals the 1-GPU run's.
 // FILE.bin = raw float32 padded mask (w+2)(h+2)(d+2) in the reference layout, e.g. dumped once from the
 // reference's STL loader (its output is not reproducible run to run).
 #include "simulation.h"
+#include "slab_hub.h"
 #include "object_loader.h"
 #include "../../include/fluid_cuda.h"
 
@@ -18,6 +21,7 @@
 #include <cstring>
 #include <fstream>
 #include <iostream>
+#include <memory>
 #include <stdexcept>
 
 static std::vector<float> analytic_mask(const std::string& kind, int w, int h, int d)
@@ -44,7 +48,7 @@ int main(int argc, char** argv)
 {
     int w = 128, h = 64, d = 64, iter = 100, acc = 15, speed = 30, dump_every = 1;   // simulation.cpp:431-436
     std::string obstacle = "none", solver = "rb", out = "data", restart, view_ppm, view_lines, view_field = "dens";
-    int view_z = -1;
+    int view_z = -1, gpus = 1;
     bool elide = false, quiet = false;
     float stl_scale = 0.8f, stl_rot[3] = { 0, 0, 0 }, stl_tr[3] = { 0, 0, 0 };      // loadSTLIntoObstacles defaults
     int stl_sampling = FLUID_VOX_HASHED;
@@ -58,7 +62,7 @@ int main(int argc, char** argv)
         else if (a == "--obstacle") obstacle = val(); else if (a == "--solver") solver = val();
         else if (a == "--out") out = val(); else if (a == "--dump-every") dump_every = std::atoi(val());
         else if (a == "--elide") elide = true; else if (a == "--quiet") quiet = true;
-        else if (a == "--restart") restart = val();
+        else if (a == "--restart") restart = val(); else if (a == "--gpus") gpus = std::atoi(val());
         else if (a == "--view-ppm") view_ppm = val(); else if (a == "--view-streamlines") view_lines = val();
         else if (a == "--view-field") view_field = val(); else if (a == "--view-z") view_z = std::atoi(val());
         else if (a == "--stl-scale") stl_scale = (float)std::atof(val());
@@ -68,8 +72,20 @@ int main(int argc, char** argv)
     }
     unsigned flags = solver == "jacobi" ? FLUID_SOLVER_JACOBI : solver == "lex" ? FLUID_SOLVER_LEX : FLUID_SOLVER_RB;
     if (elide) flags |= FLUID_ELIDE_DEAD;
+    slab::Hub* hub = nullptr;
+    if (gpus > 1) {
+        if (!view_ppm.empty() || !view_lines.empty() || (obstacle.size() > 4 && obstacle.compare(obstacle.size() - 4, 4, ".stl") == 0)) {
+            std::cerr << "fluid_tunnel: --view-* and STL voxelisation run on a single-GPU handle (omit --gpus)\n";
+            return 2;
+        }
+        hub = slab::spawn(gpus);                        // the parent stays behind as the hub and exits with the ranks' status
+        if (fluid_set_device(hub->rank) != 0) { std::cerr << "fluid_tunnel: rank " << hub->rank << ": " << fluid_last_error(nullptr) << "\n"; return 1; }
+    }
+    const bool lead = !hub || hub->rank == 0;
     try {
-        Simulation sim(w, h, d, iter, speed, 0.05f, 2.0e-5f, 1.5e-5f, acc, flags);
+        std::unique_ptr<Simulation> simp(hub ? new Simulation(*hub, w, h, d, iter, speed, 0.05f, 2.0e-5f, 1.5e-5f, acc, flags)
+                                             : new Simulation(w, h, d, iter, speed, 0.05f, 2.0e-5f, 1.5e-5f, acc, flags));
+        Simulation& sim = *simp;
         sim.quiet = quiet; sim.dump_every = dump_every > 0 ? dump_every : 1;
         sim.setOutputDirectory(out);
         if (obstacle == "sphere" || obstacle == "box") {
@@ -89,7 +105,7 @@ int main(int argc, char** argv)
             const size_t c = restart.rfind(':');
             const long k = sim.restartFromFrames(c == std::string::npos ? restart : restart.substr(0, c),
                                                  c == std::string::npos ? -1 : std::atol(restart.c_str() + c + 1));
-            if (!quiet) std::cout << "restarted from frame " << k << "\n";
+            if (!quiet && lead) std::cout << "restarted from frame " << k << "\n";
         }
         sim.run();
         if (!view_ppm.empty()) {                     // gui.py:265-300 with the viewer's fixed ranges (:272-290)
@@ -119,7 +135,7 @@ int main(int argc, char** argv)
             std::fclose(f);
             if (!quiet) std::cout << nl << " streamlines, " << np << " points -> " << view_lines << "\n";
         }
-        if (!quiet) {
+        if (!quiet && lead) {
             const double cells = (double)w * h * d;
             std::cout << fluid_version() << "\n" << sim.msPerStepLastRun() << " ms per step (incl. frame dumps), "
                       << cells / (sim.msPerStepLastRun() * 1e-3) / 1e9 << " G cell-updates/s\n";

@@ -1,6 +1,10 @@
 // simulation.cpp -- host side of the drop-in: the reference's Simulation API forwarded to libfluid_cuda.
 #include "simulation.h"
+#include "slab_hub.h"
 #include "../../include/fluid_cuda.h"
+
+#include <cstdlib>
+#include <fcntl.h>
 
 #include <iostream>
 #include <stdexcept>
@@ -18,6 +22,59 @@ Simulation::Simulation(int w, int h, int d, int iter_, int speed_, float dt_, fl
     flags = flags_;
     h_ = fluid_create(w, h, d, speed, dt, diff, visc, acc, flags);          // simulation.cpp:17-44
     if (!h_) throw std::runtime_error(std::string("fluid_create: ") + fluid_last_error(nullptr));
+    d_local_ = d;
+}
+
+// z-slab member: the C++ counterpart of fluid_simulation_b200/multi_gpu.py:attach
+Simulation::Simulation(slab::Hub& hub, int w, int h, int d, int iter_, int speed_, float dt_, float diff_, float visc_,
+                       int acc_, unsigned flags_)
+    : width(w), height(h), depth(d), speed(speed_), dt(dt_), diff(diff_), visc(visc_), acc(acc_), iter(iter_)
+{
+    flags = flags_; hub_ = &hub; rank_ = hub.rank; nranks_ = hub.nranks;
+    h_ = fluid_create_slab(w, h, d, speed, dt, diff, visc, acc, flags, rank_, nranks_);
+    if (!h_) throw std::runtime_error(std::string("fluid_create_slab: ") + fluid_last_error(nullptr));
+    check(fluid_get_dims(h_, nullptr, nullptr, nullptr, &z_lo_, &d_local_), "get_dims");
+    if (nranks_ == 1) return;
+    const char* lib = std::getenv("FLUID_NCCL_LIB");                        // default: the process's libnccl.so.2
+    // the 128-byte NCCL id of rank 0, then the collective communicator set-up
+    std::vector<char> ids((size_t)128 * nranks_), uid(128, 0);
+    if (rank_ == 0) check(fluid_comm_unique_id(lib ? lib : "", uid.data()), "comm_unique_id");
+    hub.allgather(uid.data(), 128, ids.data());
+    check(fluid_comm_init(h_, lib ? lib : "", ids.data()), "comm_init");
+    // CUDA IPC: every solver buffer and the flag block of the two z-neighbours (halos are handed over by peer
+    // stores), the advection gather sources and the flag block of every other rank
+    const size_t per = (size_t)FLUID_IPC_COUNT * 64;
+    std::vector<char> mine(per), all(per * nranks_);
+    for (int a = 0; a < FLUID_IPC_COUNT; ++a) check(fluid_ipc_export(h_, a, mine.data() + 64 * a), "ipc_export");
+    hub.allgather(mine.data(), per, all.data());
+    static const int gather_ids[5] = { FLUID_VX_PREV, FLUID_VY_PREV, FLUID_VZ_PREV, FLUID_BUFFER, FLUID_IPC_SYNC };
+    for (int r = 0; r < nranks_; ++r) {
+        if (r == rank_) continue;
+        const char* hr = all.data() + per * r;
+        if (r == rank_ - 1 || r == rank_ + 1) { for (int a = 0; a < FLUID_IPC_COUNT; ++a) check(fluid_ipc_import(h_, r, a, hr + 64 * a), "ipc_import"); }
+        else for (int a : gather_ids) check(fluid_ipc_import(h_, r, a, hr + 64 * a), "ipc_import");
+    }
+    hub.barrier();
+}
+
+// speed, dt, diff, visc and acc are public and mutable like the reference's (simulation.h:44-54)
+void Simulation::push_params() { check(fluid_set_params(h_, speed, dt, diff, visc, acc), "set_params"); }
+
+// run()'s statistics over the whole tunnel: per-slab partials folded over the ranks (sum adds, min / max fold)
+void Simulation::reduced_statistics(double out[9])
+{
+    statistics(out);
+    if (nranks_ == 1) return;
+    std::vector<double> all((size_t)9 * nranks_);
+    hub_->allgather(out, 9 * sizeof(double), all.data());
+    for (int k = 0; k < 9; ++k) {
+        double v = all[k];
+        for (int r = 1; r < nranks_; ++r) {
+            const double x = all[(size_t)9 * r + k];
+            v = k == 0 ? v + x : (k % 2 == 1 ? (x < v ? x : v) : (x > v ? x : v));      // [0] sum; odd: minima; even: maxima
+        }
+        out[k] = v;
+    }
 }
 
 Simulation::~Simulation()
@@ -116,9 +173,18 @@ void Simulation::write_pending_frame()
 {
     if (!frame_pending_) return;
     check(fluid_frame_wait(h_), "frame wait");
-    const size_t n = (size_t)(width + 2) * (height + 2) * (depth + 2);
-    for (int i = 0; i < 5; ++i)
-        if (files_[i]) std::fwrite(frame_[i], sizeof(float), n, files_[i]);  // simulation.cpp:143-147
+    const size_t plane = (size_t)(width + 2) * (height + 2);
+    if (nranks_ == 1) {
+        for (int i = 0; i < 5; ++i)
+            if (files_[i]) std::fwrite(frame_[i], sizeof(float), plane * (depth + 2), files_[i]);  // simulation.cpp:143-147
+    } else {
+        // z-slabs share the files: this rank's planes go to their place inside the frame
+        const off_t off = (off_t)((frames_written_ * (depth + 2) + own_first()) * plane * sizeof(float));
+        for (int i = 0; i < 5; ++i)
+            if (files_[i] && ::pwrite(fileno(files_[i]), frame_[i], own_count() * plane * sizeof(float), off) < 0)
+                throw std::runtime_error("frame write failed");
+    }
+    ++frames_written_;
     frame_pending_ = false;
 }
 
@@ -127,27 +193,42 @@ void Simulation::write_pending_frame()
 void Simulation::step()
 {
     flush();
+    push_params();
     check(fluid_call(h_, FLUID_OP_STEP, 0, 0, 0, 0.0f, 0.0f), "step");
     bool any = false;
     for (auto& f : files_) any = any || f;
     if (!any) return;                       // like the reference with unopened streams: no frame I/O
     write_pending_frame();
-    const size_t bytes = (size_t)(width + 2) * (height + 2) * (depth + 2) * sizeof(float);
-    for (auto& p : frame_)
-        if (!p && !(p = (float*)fluid_host_alloc(bytes))) throw std::runtime_error("pinned frame buffer allocation failed");
-    check(fluid_dump_frame_async(h_, frame_), "frame dump");
+    // pinned buffers for the planes this rank owns; the C ABI takes the base of a whole-frame buffer
+    const size_t plane = (size_t)(width + 2) * (height + 2);
+    const size_t bytes = plane * own_count() * sizeof(float);
+    float* base[5];
+    for (int i = 0; i < 5; ++i) {
+        if (!frame_[i] && !(frame_[i] = (float*)fluid_host_alloc(bytes))) throw std::runtime_error("pinned frame buffer allocation failed");
+        base[i] = frame_[i] - plane * own_first();
+    }
+    check(fluid_dump_frame_async(h_, base), "frame dump");
     frame_pending_ = true;
 }
 
 void Simulation::run()
 {
-    if (!quiet)
+    const bool lead = rank_ == 0;
+    const bool talk = !quiet && lead;
+    if (talk)
         std::cout << "starting 3-D simulation: " << width << "x" << height << "x" << depth
-                  << "  steps = " << iter << "\n";
-    // simulation.cpp:56-60; a missing directory silently disables the output, like the reference's ofstreams
+                  << "  steps = " << iter << (nranks_ > 1 ? "  (z-slabs on " + std::to_string(nranks_) + " GPUs)" : std::string()) << "\n";
+    // simulation.cpp:56-60; a missing directory silently disables the output, like the reference's ofstreams.
+    // z-slabs: rank 0 creates and truncates the files, the others open them once they exist.
     static const char* names[5] = { "data.bin", "obs.bin", "v_x.bin", "v_y.bin", "v_z.bin" };
-    for (int i = 0; i < 5; ++i) files_[i] = std::fopen((out_dir_ + "/" + names[i]).c_str(), "wb");
+    frames_written_ = 0;
+    if (lead) for (int i = 0; i < 5; ++i) files_[i] = std::fopen((out_dir_ + "/" + names[i]).c_str(), "wb");
+    if (nranks_ > 1) {
+        hub_->barrier();
+        if (!lead) for (int i = 0; i < 5; ++i) files_[i] = std::fopen((out_dir_ + "/" + names[i]).c_str(), "r+b");
+    }
     flush();
+    push_params();
     check(fluid_sync(h_), "sync");
     check(fluid_timer_start(h_), "timer");
     for (int i = 0; i < iter; ++i) {
@@ -156,8 +237,8 @@ void Simulation::run()
         if ((i + 1) % dump_every == 0) step();                                                // :71
         else check(fluid_call(h_, FLUID_OP_STEP, 0, 0, 0, 0.0f, 0.0f), "step");
         if ((i + 1) % 100 == 0 && i > 0 && !quiet) {                                          // :73-77
-            double st[9]; statistics(st);
-            std::cout << "step " << i + 1 << "\n  density sum = " << st[0] << "\n";
+            double st[9]; reduced_statistics(st);                                            // collective on z-slabs
+            if (lead) std::cout << "step " << i + 1 << "\n  density sum = " << st[0] << "\n";
         }
     }
     float ms = 0.0f;
@@ -166,7 +247,8 @@ void Simulation::run()
     write_pending_frame();
     const bool wrote = files_[0] != nullptr;
     for (auto& f : files_) if (f) { std::fclose(f); f = nullptr; }
-    if (wrote) {
+    if (nranks_ > 1) hub_->barrier();                   // every rank's planes are in the files
+    if (wrote && lead) {
         // what the reference's viewers keep in hand-synchronised constants (GUI/config.py:8-11, gui.py:32-34)
         if (std::FILE* m = std::fopen((out_dir_ + "/meta.json").c_str(), "w")) {
             std::fprintf(m, "{\n \"width\": %d, \"height\": %d, \"depth\": %d, \"padded\": [%d, %d, %d],\n \"frames\": %d, \"dump_every\": %d,"
@@ -176,8 +258,8 @@ void Simulation::run()
             std::fclose(m);
         }
     }
-    double st[9]; statistics(st);
-    if (!quiet) {                                                                             // :81-90
+    double st[9]; reduced_statistics(st);
+    if (talk) {                                                                               // :81-90
         std::cout << "\n--- statistics -------------------------------------------------\n";
         std::cout << "density  min = " << st[1] << "\n" << "density  max = " << st[2] << "\n";
         std::cout << "velocity x min = " << st[3] << "\n" << "velocity x max = " << st[4] << "\n";

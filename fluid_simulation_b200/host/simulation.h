@@ -10,6 +10,7 @@
 #include <vector>
 
 struct fluid_handle;
+namespace slab { class Hub; }
 
 class Simulation {
 private:
@@ -29,6 +30,7 @@ private:
     std::FILE* files_[5] = {};
     float* frame_[5] = {};
     bool frame_pending_ = false;
+    long frames_written_ = 0;
     void write_pending_frame();
     void check(int rc, const char* what) const;
 
@@ -39,12 +41,18 @@ public:
     float dt, diff, visc;
     int acc, iter;
 
-    /* extras of the B200 build (defaults reproduce the reference): */
+    /* extras of the B200 build.  flags = 0 selects the red-black sweep order (FLUID_SOLVER_RB), which is NOT bit-identical
+     * to the reference's single-thread lexicographic Gauss-Seidel; FLUID_SOLVER_LEX is the bit-exact mode. */
     unsigned flags = 0;          // FLUID_SOLVER_RB (default) | FLUID_SOLVER_JACOBI | FLUID_SOLVER_LEX | FLUID_ELIDE_DEAD
     int dump_every = 1;          // the reference writes a frame every step (simulation.cpp:140-148)
     bool quiet = false;
 
     Simulation(int w, int h, int d, int iter, int speed = 30, float dt = 0.05f, float diff = 2.0e-5f,
+               float visc = 1.5e-5f, int acc = 15, unsigned flags = 0);
+    /* one z-slab of a multi-GPU run (one process per GPU, host/slab_hub.h): collective over the hub's ranks.
+     * Creates the slab handle on the process's current device, attaches the NCCL communicator and maps the peers'
+     * buffers; run() then writes this rank's planes into the shared frame files and reduces the statistics. */
+    Simulation(slab::Hub& hub, int w, int h, int d, int iter, int speed = 30, float dt = 0.05f, float diff = 2.0e-5f,
                float visc = 1.5e-5f, int acc = 15, unsigned flags = 0);
     ~Simulation();
     Simulation(const Simulation&) = delete;
@@ -69,6 +77,12 @@ public:
 
 private:
     double ms_per_step_ = 0.0;
+    slab::Hub* hub_ = nullptr;   // z-slab member: rendezvous with the other ranks
+    int rank_ = 0, nranks_ = 1, z_lo_ = 1, d_local_ = 0;
+    int own_first() const { return rank_ == 0 ? 0 : z_lo_; }                                   // padded planes this rank owns
+    int own_count() const { return (rank_ == nranks_ - 1 ? depth + 1 : z_lo_ + d_local_ - 1) - own_first() + 1; }
+    void push_params();
+    void reduced_statistics(double out[9]);
 };
 
 /* loadSTLIntoObstacles (the reference's object_loader.h) lives in object_loader.h: the mesh is voxelised on

@@ -89,6 +89,9 @@ void fluid_destroy(fluid_handle*);
 
 /* parameters that the reference exposes as public data members (simulation.h:44-54) */
 int fluid_set_acc(fluid_handle*, int acc);
+/* speed, dt, diff, visc, acc are public and mutable in the reference (simulation.h:44-54: `sim.dt = ...` takes effect
+ * at the next step()); a host class that keeps them as members pushes them here before every step / run */
+int fluid_set_params(fluid_handle*, int speed, float dt, float diff, float visc, int acc);
 int fluid_get_dims(fluid_handle*, int* w, int* h, int* d, int* z_lo, int* d_local);
 
 /* whole-field transfers in reference layout (replace direct access to the std::vectors).

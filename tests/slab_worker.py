@@ -28,10 +28,10 @@ def main():
     cases = [("rb", SOLVER_RB, ORDER_RB), ("jacobi", SOLVER_JACOBI, ORDER_JACOBI)]
     # thin slabs (whole-column sweeps + hand-over kernel), thick ragged slabs (edge CTAs hand the halos over
     # inside the sweep), odd sweep counts (the solver's buffers end up permuted, on every rank alike), and the
-    # 4- and 8-warp-column kernel configurations (W > 256, W > 512)
+    # four-warp-column kernel (256 < W <= 512) and the x-tiled two-column kernel (W > 512: 516 -> 3 tiles, 772 -> 4)
     # (every slab keeps at least FL_HALO = 4 planes)
     shapes = [(24, 16, max(12, 4 * world + 1), 4), (128, 30, max(17, 5 * world), 4), (130, 9, max(9, 4 * world), 4), (256, 40, 4 * world + 3, 4), (132, 20, 35 * world + 1, 4),
-              (132, 18, 33 * world, 3), (260, 12, 33 * world + 2, 3), (516, 6, 32 * world, 4)]
+              (132, 18, 33 * world, 3), (260, 12, 33 * world + 2, 3), (516, 6, 32 * world, 4), (772, 10, 34 * world, 3)]
     for name, flag, order in cases:
         for (w, h, d, acc) in shapes:
             st = masks.random_state(w, h, d, seed=11)

@@ -172,3 +172,14 @@ def test_pair_equals_single_sweeps(monkeypatch):
     b = Simulation(w, h, d, 1, acc=acc)
     b.set("obs", obs); b.run_iterations(2)
     assert_bitwise(a.state(), b.state(), FIELD_NAMES, "pair vs single sweeps")
+
+
+@pytest.mark.parametrize("name,flag,order", SOLVERS)
+@pytest.mark.parametrize("w,h,d", [(512, 13, 9), (384, 20, 7), (260, 8, 4), (1024, 9, 4), (2052, 3, 5)])
+def test_x_tiles(monkeypatch, name, flag, order, w, h, d):
+    """Grids wider than a CTA are cut into x tiles with one redundantly computed halo quad beside every interior
+    tile edge (default above W = 512; FLUID_SW_CFG=5 forces the tiled two-column CTA from W = 260 on)."""
+    monkeypatch.setenv("FLUID_SW_CFG", "5")
+    gpu, cpu = pair(w, h, d, 3, flag, order)
+    gpu.linearSolver(1, "v_x", "v_x_prev", 0.37, 3.22); cpu.linear_solver(1, "v_x", "v_x_prev", 0.37, 3.22)
+    assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, f"x tiles [{name}] {w}x{h}x{d}")
