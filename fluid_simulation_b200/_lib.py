@@ -38,6 +38,7 @@ SYMBOLS = {
     "fluid_frame_wait": (_i, [_p]),
     "fluid_stats": (_i, [_p, _dp]),
     "fluid_divergence_norm": (_i, [_p, _dp]),
+    "fluid_stats_static": (_i, [_p, _p, _p, _p, C.c_longlong, _p, _p]),
     "fluid_render_slice": (_i, [_p, _i, _i, C.c_double, C.c_double, C.c_double, _p]),
     "fluid_density_cmap": (_i, [_dp]),
     "fluid_streamlines": (_i, [_p, _p, _i, C.c_longlong, _ip, C.POINTER(C.c_longlong), _p, _p, _p]),

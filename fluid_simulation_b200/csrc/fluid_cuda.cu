@@ -12,6 +12,7 @@
 #include <cstring>
 #include <new>
 #include <unordered_map>
+#include <mutex>
 
 thread_local std::string g_fluid_create_error;
 
@@ -270,3 +271,82 @@ int fluid_profile_read(fluid_handle* h, double out[3])
 
 #include "api_io.inl"
 #include "api_ops.inl"
+
+// ---- fluid_stats_static: run()'s statistics without any allocation ------------------------------------
+// No counterpart in the reference; added for callers that cannot
+// call cudaMalloc (CUDA graph capture, tight serving loops).  Same two-pass reduction as fluid_stats
+// (k_stats_final is shared), but the per-block partials live in a file-scope device array instead of the
+// handle's cudaMalloc'ed d_partial, and the fields are the caller's flat device arrays.
+#define FL_STATIC_CHUNK      65536                  // cells folded by one block
+#define FL_STATIC_MAX_BLOCKS 4096                   // => at most 2^28 cells per call
+#define FL_STATIC_MAX_DEVICES 64
+// 4096 x 9 doubles = 288 KiB, held by every GPU that loads the library until the process exits
+static __device__ __align__(256) double g_static_partials[FL_STATIC_MAX_BLOCKS * FL_NSTAT];
+// the array's DEVICE address per device (the name above is only a host-side stand-in in host code)
+static double* g_static_partials_addr[FL_STATIC_MAX_DEVICES];
+static std::mutex g_static_mutex;
+
+// block b folds cells [b*CHUNK, min(n, (b+1)*CHUNK)) of the four flat arrays
+__global__ void __launch_bounds__(256) k_stats_flat_partial(long long n, const float* __restrict__ dens,
+                                                            const float* __restrict__ vx,
+                                                            const float* __restrict__ vy,
+                                                            const float* __restrict__ vz,
+                                                            double* __restrict__ partial)
+{
+    const long long lo = (long long)blockIdx.x * FL_STATIC_CHUNK;
+    const long long hi = lo + FL_STATIC_CHUNK < n ? lo + FL_STATIC_CHUNK : n;
+    double s = 0.0;
+    float mn[4] = { FLT_MAX, FLT_MAX, FLT_MAX, FLT_MAX }, mx[4] = { -FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    for (long long c = lo + threadIdx.x; c < hi; c += blockDim.x) {
+        const float d = dens[c], a = vx[c], b = vy[c], e = vz[c];
+        s += (double)d;
+        mn[0] = fminf(mn[0], d); mx[0] = fmaxf(mx[0], d);
+        mn[1] = fminf(mn[1], a); mx[1] = fmaxf(mx[1], a);
+        mn[2] = fminf(mn[2], b); mx[2] = fmaxf(mx[2], b);
+        mn[3] = fminf(mn[3], e); mx[3] = fmaxf(mx[3], e);
+    }
+    block_fold_stats(s, mn, mx, partial + (long long)blockIdx.x * FL_NSTAT);
+}
+
+// set-up, once per device, with that device current: the device address of g_static_partials
+static int fl_static_scratch(double** out)
+{
+    int dev = -1;
+    FL_CUDA(nullptr, cudaGetDevice(&dev));
+    if (dev < 0 || dev >= FL_STATIC_MAX_DEVICES)
+        return fl_fail(nullptr, FLUID_E_ARG, "fluid_stats_static: device ordinal %d outside 0..%d", dev,
+                       FL_STATIC_MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_partials_addr[dev]) {
+        double* p = nullptr;
+        FL_CUDA(nullptr, cudaGetSymbolAddress((void**)&p, g_static_partials));
+        if (!p) return fl_fail(nullptr, FLUID_E_CUDA, "fluid_stats_static: cudaGetSymbolAddress returned NULL");
+        g_static_partials_addr[dev] = p;
+    }
+    *out = g_static_partials_addr[dev];
+    return 0;
+}
+
+extern "C" int fluid_stats_static(const float* dens, const float* v_x, const float* v_y, const float* v_z,
+                                  long long n_cells, double* out_device, void* stream)
+{
+    if (!dens || !v_x || !v_y || !v_z || !out_device)
+        return fl_fail(nullptr, FLUID_E_ARG, "fluid_stats_static: NULL field or output pointer");
+    const long long max_cells = (long long)FL_STATIC_MAX_BLOCKS * FL_STATIC_CHUNK;
+    if (n_cells < 1 || n_cells > max_cells)
+        return fl_fail(nullptr, FLUID_E_ARG,
+                       "fluid_stats_static: n_cells = %lld outside 1..%lld (the static scratch holds %d block "
+                       "partials of %d cells each; use fluid_stats for larger volumes)",
+                       n_cells, max_cells, FL_STATIC_MAX_BLOCKS, FL_STATIC_CHUNK);
+    double* partial = nullptr;
+    if (int e = fl_static_scratch(&partial)) return e;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int nb = (int)((n_cells + FL_STATIC_CHUNK - 1) / FL_STATIC_CHUNK);
+    // every partial the second pass reads is written by the first pass of the SAME call: nothing in the
+    // shared array has to start at zero, and what the previous call left there is never read
+    k_stats_flat_partial<<<nb, 256, 0, s>>>(n_cells, dens, v_x, v_y, v_z, partial);
+    FL_CUDA(nullptr, cudaGetLastError());
+    k_stats_final<<<1, 256, 0, s>>>(nb, partial, out_device);
+    FL_CUDA(nullptr, cudaGetLastError());
+    return 0;
+}

@@ -143,6 +143,23 @@ int fluid_stats(fluid_handle*, double out[9]);
 /* sqrt(sum div^2) and max|div| of the stored divergence field over interior fluid cells */
 int fluid_divergence_norm(fluid_handle*, double out[2]);
 
+/* fluid_stats without a handle and WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  dens, v_x, v_y, v_z: DEVICE pointers to n_cells floats each
+ * (e.g. the reference's padded arrays, (w+2)(h+2)(d+2) cells); out_device: DEVICE pointer to 9 doubles, laid out
+ * as fluid_stats' out; stream: a cudaStream_t of the current device (NULL = the default stream).  Asynchronous:
+ * two kernels are queued on `stream`, nothing is synchronised, and no cudaMalloc / cudaFree or other allocating
+ * routine is called.  The per-block partials live in a file-scope device array of 4096 x 9 doubles (288 KiB
+ * that every GPU loading the library holds until the process exits), one block per 65536 cells, hence
+ *     n_cells <= FLUID_STATS_STATIC_MAX_CELLS = 2^28;  larger (or n_cells < 1) fails with FLUID_E_ARG
+ * and a text in fluid_last_error(NULL).  The array is SHARED by all calls on a device: calls that overlap on
+ * the GPU (different streams, different threads) race on it -- order them on one stream or with events.
+ * Nothing in it has to start at zero (each call overwrites every partial it reads).  The first call on a
+ * device looks the array's device address up (cudaGetSymbolAddress): make that call before a capture begins. */
+#define FLUID_STATS_STATIC_MAX_CELLS (1LL << 28)
+int fluid_stats_static(const float* dens, const float* v_x, const float* v_y, const float* v_z,
+                       long long n_cells, double* out_device, void* stream);
+
 /* ---- the offline viewers' arithmetic on the resident fields; single-GPU handles only.
  * The viewers' Qt windows and OpenGL draw calls are not reproduced: these return what they would draw. ---- */
 
