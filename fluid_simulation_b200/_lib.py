@@ -42,6 +42,7 @@ SYMBOLS = {
     "fluid_render_slice": (_i, [_p, _i, _i, C.c_double, C.c_double, C.c_double, _p]),
     "fluid_density_cmap": (_i, [_dp]),
     "fluid_streamlines": (_i, [_p, _p, _i, C.c_longlong, _ip, C.POINTER(C.c_longlong), _p, _p, _p]),
+    "fluid_obstacle_mesh": (_i, [_p, C.c_double, C.c_longlong, C.c_longlong, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), _p, _p]),
     "fluid_sync": (_i, [_p]),
     "fluid_last_error": (C.c_char_p, [_p]),
     "fluid_host_alloc": (_p, [C.c_size_t]),

@@ -114,6 +114,12 @@ int fluid_density_cmap(double lut[768])
     return 0;
 }
 
+int fluid_obstacle_mesh(fluid_handle* h, double level, long long max_verts, long long max_faces, long long* n_verts,
+                        long long* n_faces, float* verts, int* faces)
+{
+    return fl_obstacle_mesh(h, level, max_verts, max_faces, n_verts, n_faces, verts, faces);
+}
+
 int fluid_streamlines(fluid_handle* h, const fluid_streamline_params* params, int max_lines, long long max_points,
                       int* n_lines, long long* n_points, int* line_len, double* norm_speed, double* points)
 {
@@ -246,12 +252,11 @@ int fluid_stats(fluid_handle* h, double out[9])
     if (!h || !out) return FLUID_E_ARG;
     const int first = (h->rank == 0) ? 0 : 1;
     const int last = (h->rank == h->nranks - 1) ? h->g.Dl + 1 : h->g.Dl;
-    const long long n = (long long)(h->g.W + 2) * h->g.rows * (last - first + 1);
-    const int nb = fl_grid_1d(n, 256, h->n_partial);
-    k_stats_partial<<<nb, 256, 0, h->stream>>>(h->g, first, last, h->field[FLUID_DENS], h->field[FLUID_VX],
-                                               h->field[FLUID_VY], h->field[FLUID_VZ], h->d_partial);
-    FL_CHECK_LAUNCH(h);
-    k_stats_final<<<1, 256, 0, h->stream>>>(nb, h->d_partial, h->d_out);
+    const long long nq = (h->g.plane >> 2) * (last - first + 1);
+    const int nb = fl_grid_1d(nq, 256, h->n_partial);
+    k_stats_quads<<<nb, 256, 0, h->stream>>>(h->g, first, last, h->field[FLUID_DENS], h->field[FLUID_VX],
+                                             h->field[FLUID_VY], h->field[FLUID_VZ], h->d_partial,
+                                             reinterpret_cast<unsigned*>(h->d_out + FL_NSTAT), h->d_out);
     FL_CHECK_LAUNCH(h);
     FL_CUDA(h, cudaMemcpyAsync(out, h->d_out, FL_NSTAT * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     FL_CUDA(h, cudaStreamSynchronize(h->stream));

@@ -38,6 +38,7 @@ int fluid_call(fluid_handle* h, int op, int b, int field_id, int prev_id, float 
         case FLUID_OP_INFLOW_VEL:  return fl_inflow_velocity(h);
         case FLUID_OP_STEP:        return fl_step_only(h);
         case FLUID_OP_COPY:        return fl_copy_field(h, field_id, prev_id);
+        case FLUID_OP_ADVECT_VEL:  return fl_advect_velocity(h);
     }
     return fl_fail(h, FLUID_E_ARG, "fluid_call: unknown op %d", op);
 }

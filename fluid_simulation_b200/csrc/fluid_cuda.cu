@@ -9,6 +9,7 @@
 #include "comm.cuh"
 #include "voxelize.cuh"
 #include "postproc.cuh"
+#include "mesh.cuh"
 #include <cstring>
 #include <new>
 #include <unordered_map>
@@ -56,7 +57,8 @@ static int alloc_all(fluid_handle* h)
     FL_CUDA(h, cudaMalloc(&h->staging, ref_plane_floats(h->g) * (h->g.Dl + 2 * FL_HALO) * sizeof(float)));
     h->n_partial = 148 * 8;
     FL_CUDA(h, cudaMalloc(&h->d_partial, (size_t)h->n_partial * FL_NSTAT * sizeof(double)));
-    FL_CUDA(h, cudaMalloc(&h->d_out, FL_NSTAT * sizeof(double)));
+    FL_CUDA(h, cudaMalloc(&h->d_out, (FL_NSTAT + 1) * sizeof(double)));        // + the statistics kernel's ticket
+    FL_CUDA(h, cudaMemsetAsync(h->d_out, 0, (FL_NSTAT + 1) * sizeof(double), h->stream));
     FL_CUDA(h, cudaMalloc(&h->d_sync, 64 * sizeof(unsigned)));
     FL_CUDA(h, cudaMemsetAsync(h->d_sync, 0, 64 * sizeof(unsigned), h->stream));
     return 0;
@@ -274,9 +276,9 @@ int fluid_profile_read(fluid_handle* h, double out[3])
 
 // ---- fluid_stats_static: run()'s statistics without any allocation ------------------------------------
 // No counterpart in the reference; added for callers that cannot
-// call cudaMalloc (CUDA graph capture, tight serving loops).  Same two-pass reduction as fluid_stats
-// (k_stats_final is shared), but the per-block partials live in a file-scope device array instead of the
-// handle's cudaMalloc'ed d_partial, and the fields are the caller's flat device arrays.
+// call cudaMalloc (CUDA graph capture, tight serving loops).  A two-pass reduction with fluid_stats' block
+// fold, but the per-block partials live in a file-scope device array instead of the handle's cudaMalloc'ed
+// d_partial, and the fields are the caller's flat device arrays.
 #define FL_STATIC_CHUNK      65536                  // cells folded by one block
 #define FL_STATIC_MAX_BLOCKS 4096                   // => at most 2^28 cells per call
 #define FL_STATIC_MAX_DEVICES 64

@@ -1,5 +1,5 @@
 // kernels_reduce.cuh -- run()'s statistics (simulation.cpp:73-90) and divergence norms as
-// warp-shuffle block reductions; one partial per block, folded by a single-block second pass.
+// warp-shuffle block reductions; one partial per block, folded by the last block to finish.
 #pragma once
 #include "common.cuh"
 #include <float.h>
@@ -58,37 +58,7 @@ __device__ __forceinline__ void block_fold_stats(double s, const float mn[4], co
     }
 }
 
-// pass 1: every padded cell this slab OWNS (local planes zl_first..zl_last, all x in 0..W+1, y in 0..H+1)
-__global__ void __launch_bounds__(256) k_stats_partial(Grid g, int zl_first, int zl_last,
-                                                       const float* __restrict__ dens,
-                                                       const float* __restrict__ vx,
-                                                       const float* __restrict__ vy,
-                                                       const float* __restrict__ vz,
-                                                       double* __restrict__ partial)
-{
-    // one x-row of the padded volume per block iteration: the division by the row length happens once
-    // per row, not once per cell (the kernel was bound by integer divides)
-    const int Wp = g.W + 2;
-    const long long nrows = (long long)g.rows * (zl_last - zl_first + 1);
-    double s = 0.0;
-    float mn[4] = { FLT_MAX, FLT_MAX, FLT_MAX, FLT_MAX }, mx[4] = { -FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX };
-    for (long long r = blockIdx.x; r < nrows; r += gridDim.x) {
-        const int y = (int)(r % g.rows), zl = zl_first + (int)(r / g.rows);
-        const long long c0 = fl_idx(g, 0, y, zl);
-        for (int x = threadIdx.x; x < Wp; x += blockDim.x) {
-            const long long c = c0 + x;
-            float d = dens[c], a = vx[c], b = vy[c], e = vz[c];
-            s += (double)d;
-            mn[0] = fminf(mn[0], d); mx[0] = fmaxf(mx[0], d);
-            mn[1] = fminf(mn[1], a); mx[1] = fmaxf(mx[1], a);
-            mn[2] = fminf(mn[2], b); mx[2] = fmaxf(mx[2], b);
-            mn[3] = fminf(mn[3], e); mx[3] = fmaxf(mx[3], e);
-        }
-    }
-    block_fold_stats(s, mn, mx, partial + (long long)blockIdx.x * FL_NSTAT);
-}
-
-// pass 2: one block folds the per-block partials
+// one block folds per-block partials (second pass of fluid_stats_static)
 __global__ void __launch_bounds__(256) k_stats_final(int nblocks, const double* __restrict__ partial,
                                                      double* __restrict__ out)
 {
@@ -104,6 +74,72 @@ __global__ void __launch_bounds__(256) k_stats_final(int nblocks, const double* 
         }
     }
     block_fold_stats(s, mn, mx, out);
+}
+
+// ---- one launch: float4 loads over whole planes, the last block to finish folds the partials ----------
+// A plane is a contiguous run of pitch*rows floats and a row holds its W+2 cells at float offsets
+// FL_XOFF .. FL_XOFF+W+1, so the owned planes are streamed as float4 quads and the pitch padding is masked
+// by the quad's position in its row (kept incrementally: no division in the loop).  `ticket` must be zero
+// on entry and is zero again on exit.
+__device__ __forceinline__ void fl_stat_acc(bool on, float d, float a, float b, float e, double& s, float mn[4], float mx[4])
+{
+    if (!on) return;
+    s += (double)d;
+    mn[0] = fminf(mn[0], d); mx[0] = fmaxf(mx[0], d);
+    mn[1] = fminf(mn[1], a); mx[1] = fmaxf(mx[1], a);
+    mn[2] = fminf(mn[2], b); mx[2] = fmaxf(mx[2], b);
+    mn[3] = fminf(mn[3], e); mx[3] = fmaxf(mx[3], e);
+}
+
+__global__ void __launch_bounds__(256) k_stats_quads(Grid g, int zl_first, int zl_last,
+                                                     const float* __restrict__ dens, const float* __restrict__ vx,
+                                                     const float* __restrict__ vy, const float* __restrict__ vz,
+                                                     double* partial, unsigned* ticket, double* out)
+{
+    const int qpr = g.pitch >> 2;                                   // quads per row
+    const long long base = (long long)zl_first * g.plane;           // float offset of the first owned plane
+    const long long nq = ((long long)(zl_last - zl_first + 1) * g.plane) >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const int dcol = (int)(stride % qpr);
+    const int last_f = FL_XOFF + g.W + 1;                           // float offset of cell x = W+1 in its row
+    const float4* D = reinterpret_cast<const float4*>(dens + base);
+    const float4* X = reinterpret_cast<const float4*>(vx + base);
+    const float4* Y = reinterpret_cast<const float4*>(vy + base);
+    const float4* Z = reinterpret_cast<const float4*>(vz + base);
+    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    int col = (int)(q % qpr);
+    double s = 0.0;
+    float mn[4] = { FLT_MAX, FLT_MAX, FLT_MAX, FLT_MAX }, mx[4] = { -FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    for (; q < nq; q += stride) {
+        const float4 d = D[q], a = X[q], b = Y[q], e = Z[q];
+        const int f0 = col << 2;
+        fl_stat_acc(f0     >= FL_XOFF && f0     <= last_f, d.x, a.x, b.x, e.x, s, mn, mx);
+        fl_stat_acc(f0 + 1 >= FL_XOFF && f0 + 1 <= last_f, d.y, a.y, b.y, e.y, s, mn, mx);
+        fl_stat_acc(f0 + 2 >= FL_XOFF && f0 + 2 <= last_f, d.z, a.z, b.z, e.z, s, mn, mx);
+        fl_stat_acc(f0 + 3 >= FL_XOFF && f0 + 3 <= last_f, d.w, a.w, b.w, e.w, s, mn, mx);
+        col += dcol; if (col >= qpr) col -= qpr;
+    }
+    block_fold_stats(s, mn, mx, partial + (long long)blockIdx.x * FL_NSTAT);
+    __shared__ bool is_last;
+    if (threadIdx.x == 0) {
+        __threadfence();                                            // this block's partials before its ticket
+        is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { mn[k] = FLT_MAX; mx[k] = -FLT_MAX; }
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) {
+        const double* p = partial + (long long)i * FL_NSTAT;     // written by other SMs: read at L2
+        s += __ldcg(p);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { mn[k] = fminf(mn[k], (float)__ldcg(p + 1 + 2 * k)); mx[k] = fmaxf(mx[k], (float)__ldcg(p + 2 + 2 * k)); }
+    }
+    __syncthreads();                                                // block_fold_stats reuses its shared array
+    block_fold_stats(s, mn, mx, out);
+    if (threadIdx.x == 0) *ticket = 0u;
 }
 
 // sum(div^2) and max|div| over interior fluid cells; partial[2*block] = sum, [2*block+1] = max

@@ -5,6 +5,7 @@
 // reference's operand order so results are bit-identical to the CPU code.
 #pragma once
 #include "common.cuh"
+#include "recip_div.h"
 
 struct Quad7 { float c[4], xm, xp, yp[4], ym[4], zp[4], zm[4]; };
 
@@ -124,12 +125,22 @@ __global__ void __launch_bounds__(256) k_divergence(Grid g, const float* __restr
 // division it replaces is ~15 instructions on its fast path and a ~100-instruction subroutine whenever the
 // numerator is zero or denormal -- which the far field of the pressure solve is full of.  Otherwise
 // s1 = h, s2 = 2h and the division stays.
-template <bool POW2>
-__device__ __forceinline__ float fl_axis_grad(bool po, bool mo, float pp, float pc, float pm, float s1, float s2)
+// Any other h: FL_GRAD_RECIP divides by multiplying with the correctly rounded reciprocal and one FMA
+// correction (recip_div.h; verified bit-identical to the division for the launch's two divisors on the host
+// before the first launch); FL_GRAD_DIV keeps the division (A/B, or a divisor that failed the verification).
+enum { FL_GRAD_DIV = 0, FL_GRAD_POW2 = 1, FL_GRAD_RECIP = 2 };
+struct GradScale { float s1, s2, r1, r2; };          // h, 2h and (POW2, RECIP) their reciprocals
+
+template <int MODE>
+__device__ __forceinline__ float fl_axis_grad(bool po, bool mo, float pp, float pc, float pm, const GradScale& k)
 {
     const float hi = po ? pp : pc, lo = mo ? pm : pc;
-    const float sc = (po && mo) ? s2 : s1;
-    const float q = POW2 ? (hi - lo) * sc : (hi - lo) / sc;
+    const bool both = po && mo;
+    const float n = hi - lo;
+    float q;
+    if (MODE == FL_GRAD_POW2)       q = n * (both ? k.r2 : k.r1);
+    else if (MODE == FL_GRAD_RECIP) q = fl_recip_div(n, both ? k.s2 : k.s1, both ? k.r2 : k.r1);
+    else                            q = n / (both ? k.s2 : k.s1);
     return (po || mo) ? q : 0.0f;
 }
 
@@ -137,11 +148,11 @@ __device__ __forceinline__ float fl_axis_grad(bool po, bool mo, float pp, float 
 #define FL_QBIT(f4, i, m) (((f4) & ((unsigned)(m) << (8 * (i)))) != 0u)
 
 // ---- project part 3: v -= grad p on fluid cells, then setBounds(1..3) (:322-361) -------------
-template <bool POW2>
+template <int MODE>
 __global__ void __launch_bounds__(256) k_gradient(Grid g, const float* __restrict__ p,
                                                   const unsigned char* __restrict__ flags,
                                                   float* __restrict__ vx, float* __restrict__ vy,
-                                                  float* __restrict__ vz, float s1, float s2)
+                                                  float* __restrict__ vz, GradScale sc)
 {
     QuadPos qp = fl_quad_pos(g, 1 + blockIdx.z);
     if (!qp.valid) return;
@@ -155,9 +166,9 @@ __global__ void __launch_bounds__(256) k_gradient(Grid g, const float* __restric
     for (int i = 0; i < 4; ++i) {
         const float pxp = (i == 3) ? q.xp : q.c[i + 1];
         const float pxm = (i == 0) ? q.xm : q.c[i - 1];
-        const float gx = fl_axis_grad<POW2>(FL_QBIT(f4, i, FL_OPEN_XP), FL_QBIT(f4, i, FL_OPEN_XM), pxp, q.c[i], pxm, s1, s2);
-        const float gy = fl_axis_grad<POW2>(FL_QBIT(f4, i, FL_OPEN_YP), FL_QBIT(f4, i, FL_OPEN_YM), q.yp[i], q.c[i], q.ym[i], s1, s2);
-        const float gz = fl_axis_grad<POW2>(FL_QBIT(f4, i, FL_OPEN_ZP), FL_QBIT(f4, i, FL_OPEN_ZM), q.zp[i], q.c[i], q.zm[i], s1, s2);
+        const float gx = fl_axis_grad<MODE>(FL_QBIT(f4, i, FL_OPEN_XP), FL_QBIT(f4, i, FL_OPEN_XM), pxp, q.c[i], pxm, sc);
+        const float gy = fl_axis_grad<MODE>(FL_QBIT(f4, i, FL_OPEN_YP), FL_QBIT(f4, i, FL_OPEN_YM), q.yp[i], q.c[i], q.ym[i], sc);
+        const float gz = fl_axis_grad<MODE>(FL_QBIT(f4, i, FL_OPEN_ZP), FL_QBIT(f4, i, FL_OPEN_ZM), q.zp[i], q.c[i], q.zm[i], sc);
         const bool solid = FL_QBIT(f4, i, FL_SOLID);              // :326 solids keep their value
         rx[i] = solid ? rx[i] : rx[i] - gx;
         ry[i] = solid ? ry[i] : ry[i] - gy;
@@ -355,5 +366,161 @@ __global__ void __launch_bounds__(256) k_advect_rows(Grid g, int b, float* __res
             if (gz == 1)   field[c - plane] = gzv;                           // :208-214
             if (gz == g.D) field[c + plane] = gzv;
         }
+    }
+}
+
+// ---- the three velocity advections of step() (simulation.cpp:125-127) in ONE launch ------------------------
+// advect(1, v_x, v_x_prev); advect(2, v_y, v_y_prev); advect(3, v_z, v_z_prev) read the velocity of the
+// OTHER components only at their own cell (:380-382) and gather only from the *_prev copies, which none of
+// them writes.  What call 2 reads of v_x at its own cell is what call 1 + setBounds(1) left there, and an
+// interior cell's value after setBounds is its advected value, or zero where the zero mask of component 1
+// says so -- computable in the thread.  So one thread produces v_x, then v_y from it, then v_z from both:
+// one flag load, five own-cell loads instead of nine, one index set-up, three gathers, three stores,
+// 32 instead of 48 B per cell.  Statements and operand order per component are those of k_advect_rows:
+// bit-identical to the three launches (tests/test_gpu_parity.py).
+struct GatherSrc3 { const float* base[3][8]; int zlo[8]; int dl[8]; int n; };
+
+struct AdvConst {
+    float kx, ky, kz, hx, hy, hz;
+    unsigned pitch, plane;
+    int zoff;
+};
+
+// back-trace from (fx, fy, fz) with velocity (vx, vy, vz), gather the 8 corners from component `comp`'s source
+template <bool SLAB>
+__device__ __forceinline__ void fl_adv_gather(const Grid& g, const GatherSrc3& src, int comp, const AdvConst& k,
+                                              float fx, float fy, float fz, float vx, float vy, float vz,
+                                              float& sx, float& sy, float& sz, float q[8])
+{
+    float xb = fx - k.kx * vx;                                               // :384-386
+    float yb = fy - k.ky * vy;
+    float zb = fz - k.kz * vz;
+    xb = fl_clamp(xb, 0.5f, k.hx);                                           // :388-390
+    yb = fl_clamp(yb, 0.5f, k.hy);
+    zb = fl_clamp(zb, 0.5f, k.hz);
+    const float fi = floorf(xb), fj = floorf(yb), fk = floorf(zb);           // :392-397
+    sx = xb - fi; sy = yb - fj; sz = zb - fk;                                // :399-401
+    const int i0 = (int)fi, j0 = (int)fj, k0 = (int)fk;
+    if (SLAB) {
+        int r0 = 0, r1 = 0;
+#pragma unroll 1
+        for (int t = 0; t < src.n - 1; ++t) {
+            if (k0 >= src.zlo[t] + src.dl[t]) r0 = t + 1;
+            if (k0 + 1 >= src.zlo[t] + src.dl[t]) r1 = t + 1;
+        }
+        const int o = FL_XOFF + i0 + j0 * (int)k.pitch;
+        const float* __restrict__ q0 = src.base[comp][r0] + ((long long)(k0 - src.zlo[r0] + 1) * g.plane + o);
+        const float* __restrict__ q1 = src.base[comp][r1] + ((long long)(k0 + 1 - src.zlo[r1] + 1) * g.plane + o);
+        q[0] = fl_ldnc(q0); q[1] = fl_ldnc(q0 + 1); q[2] = fl_ldnc(q0 + k.pitch); q[3] = fl_ldnc(q0 + k.pitch + 1);
+        q[4] = fl_ldnc(q1); q[5] = fl_ldnc(q1 + 1); q[6] = fl_ldnc(q1 + k.pitch); q[7] = fl_ldnc(q1 + k.pitch + 1);
+    } else {
+        const float* __restrict__ gs = src.base[comp][0];
+        const unsigned o00 = FL_XOFF + (unsigned)i0 + (unsigned)j0 * k.pitch + (unsigned)(k0 + k.zoff) * k.plane;
+        const unsigned o10 = o00 + k.pitch, o01 = o00 + k.plane, o11 = o01 + k.pitch;
+        q[0] = fl_ldnc(gs + o00); q[1] = fl_ldnc(gs + o00 + 1); q[2] = fl_ldnc(gs + o10); q[3] = fl_ldnc(gs + o10 + 1);
+        q[4] = fl_ldnc(gs + o01); q[5] = fl_ldnc(gs + o01 + 1); q[6] = fl_ldnc(gs + o11); q[7] = fl_ldnc(gs + o11 + 1);
+    }
+}
+
+__device__ __forceinline__ float fl_adv_lerp(const float q[8], float sx, float sy, float sz)
+{
+    const float tx = 1.0f - sx, ty = 1.0f - sy, tz = 1.0f - sz;
+    const float c00 = q[0] * tx + q[1] * sx;                                 // :412-415  (c000, c100)
+    const float c01 = q[4] * tx + q[5] * sx;                                 //           (c001, c101)
+    const float c10 = q[2] * tx + q[3] * sx;                                 //           (c010, c110)
+    const float c11 = q[6] * tx + q[7] * sx;                                 //           (c011, c111)
+    const float e0 = c00 * ty + c10 * sy;                                    // :417-418
+    const float e1 = c01 * ty + c11 * sy;
+    return e0 * tz + e1 * sz;                                                // :420
+}
+
+// the ghosts next to a cell on a domain face: setBounds(b, field) (:183-246) copies the cell's PRE-zero value
+// (negated for the wall-normal component).  Out of line: one branch per row instead of 18 predicated stores.
+__device__ __noinline__ void fl_adv_ghosts(int W, int H, int D, float* __restrict__ f1, float* __restrict__ f2,
+                                           float* __restrict__ f3, unsigned c, float r1, float r2, float r3,
+                                           int x, int y, int gz, unsigned pitch, unsigned plane)
+{
+    if (x == 1)   { f1[c - 1] = -r1; f2[c - 1] = r2; f3[c - 1] = r3; }       // :189
+    if (x == W)   { f1[c + 1] = r1;  f2[c + 1] = r2; f3[c + 1] = r3; }       // :191
+    if (y == 1)   { f1[c - pitch] = r1; f2[c - pitch] = -r2; f3[c - pitch] = r3; }   // :198-201
+    if (y == H)   { f1[c + pitch] = r1; f2[c + pitch] = -r2; f3[c + pitch] = r3; }
+    if (gz == 1)  { f1[c - plane] = r1; f2[c - plane] = r2; f3[c - plane] = -r3; }   // :208-214
+    if (gz == D)  { f1[c + plane] = r1; f2[c + plane] = r2; f3[c + plane] = -r3; }
+}
+
+template <bool SLAB, int NY>
+__global__ void __launch_bounds__(256) k_advect3(Grid g, float* __restrict__ vxf, float* __restrict__ vyf,
+                                                 float* __restrict__ vzf, const float* __restrict__ vxp,
+                                                 const float* __restrict__ vyp, const float* __restrict__ vzp,
+                                                 GatherSrc3 src, const unsigned char* __restrict__ flags, float dt)
+{
+    const int x = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+    const int ya = 1 + (blockIdx.y * blockDim.y + threadIdx.y) * NY;
+    const int zl = 1 + blockIdx.z;
+    if (x > g.W || ya > g.H) return;
+    const int gz = g.zlo + zl - 1;
+    const float fW = (float)g.W, fH = (float)g.H, fD = (float)g.D;
+    AdvConst k;
+    k.kx = dt * fW; k.ky = dt * fH; k.kz = dt * fD;                          // dt * width etc. (:384-386, left to right)
+    k.hx = fW + 0.5f; k.hy = fH + 0.5f; k.hz = fD + 0.5f;
+    k.pitch = (unsigned)g.pitch; k.plane = (unsigned)g.plane;
+    k.zoff = 1 - src.zlo[0];
+    const bool xz_edge = x == 1 || x == g.W || gz == 1 || gz == g.D;
+    const float fx = (float)x, fz = (float)gz;
+    const unsigned c0 = FL_XOFF + (unsigned)x + (unsigned)ya * k.pitch + (unsigned)zl * k.plane;
+    // own-cell loads of every row first, then per component: all gathers of all rows in flight together
+    unsigned cc[NY], fl[NY];
+    float ox[NY], oy[NY], oz[NY], py[NY], pz[NY], fy[NY];
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {
+        const bool in = ya + j <= g.H;                                       // rows past H repeat row ya and are not stored
+        cc[j] = in ? c0 + (unsigned)j * k.pitch : c0;
+        fy[j] = (float)(in ? ya + j : ya);
+        fl[j] = flags[cc[j]];
+        ox[j] = vxp[cc[j]]; oy[j] = vyf[cc[j]]; oz[j] = vzf[cc[j]];          // advect(1): v_x_prev, v_y, v_z (:380-382)
+        py[j] = vyp[cc[j]]; pz[j] = vzp[cc[j]];
+    }
+    float sx[NY], sy[NY], sz[NY], q[NY][8], r1[NY], r2[NY], r3[NY];
+    // solid cells back-trace with zero velocity (their result is discarded, :375-378): the gather stays inside the volume
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {
+        const bool solid = fl[j] & FL_SOLID;
+        fl_adv_gather<SLAB>(g, src, 0, k, fx, fy[j], fz, solid ? 0.0f : ox[j], solid ? 0.0f : oy[j], solid ? 0.0f : oz[j],
+                            sx[j], sy[j], sz[j], q[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {
+        r1[j] = (fl[j] & FL_SOLID) ? 0.0f : fl_adv_lerp(q[j], sx[j], sy[j], sz[j]);
+        ox[j] = (fl[j] & fl_zero_mask(1)) ? 0.0f : r1[j];                    // v_x at this cell after advect(1) + setBounds(1)
+    }
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {                                           // advect(2): v_x (new), v_y_prev, v_z
+        const bool solid = fl[j] & FL_SOLID;
+        fl_adv_gather<SLAB>(g, src, 1, k, fx, fy[j], fz, solid ? 0.0f : ox[j], solid ? 0.0f : py[j], solid ? 0.0f : oz[j],
+                            sx[j], sy[j], sz[j], q[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {
+        r2[j] = (fl[j] & FL_SOLID) ? 0.0f : fl_adv_lerp(q[j], sx[j], sy[j], sz[j]);
+        oy[j] = (fl[j] & fl_zero_mask(2)) ? 0.0f : r2[j];
+    }
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {                                           // advect(3): v_x (new), v_y (new), v_z_prev
+        const bool solid = fl[j] & FL_SOLID;
+        fl_adv_gather<SLAB>(g, src, 2, k, fx, fy[j], fz, solid ? 0.0f : ox[j], solid ? 0.0f : oy[j], solid ? 0.0f : pz[j],
+                            sx[j], sy[j], sz[j], q[j]);
+    }
+    asm volatile("" ::: "memory");     // every gather is issued before the first store
+#pragma unroll
+    for (int j = 0; j < NY; ++j) {
+        const int y = ya + j;
+        if (y > g.H) break;
+        r3[j] = (fl[j] & FL_SOLID) ? 0.0f : fl_adv_lerp(q[j], sx[j], sy[j], sz[j]);
+        const unsigned c = cc[j];
+        vxf[c] = (fl[j] & fl_zero_mask(1)) ? 0.0f : r1[j];
+        vyf[c] = (fl[j] & fl_zero_mask(2)) ? 0.0f : r2[j];
+        vzf[c] = (fl[j] & fl_zero_mask(3)) ? 0.0f : r3[j];
+        if (xz_edge || y == 1 || y == g.H)
+            fl_adv_ghosts(g.W, g.H, g.D, vxf, vyf, vzf, c, r1[j], r2[j], r3[j], x, y, gz, k.pitch, k.plane);
     }
 }

@@ -9,6 +9,8 @@
 #include <math.h>
 #include <string.h>
 #include <stdlib.h>
+#include <mutex>
+#include <unordered_map>
 
 int fl_halo_exchange(fluid_handle* h, int n, float* const* fields);      // comm.cuh (slab mode)
 int fl_lex_solve(fluid_handle* h, int nb, const int* b, const int* fid, const int* pid,
@@ -175,6 +177,18 @@ static inline int fl_divergence(fluid_handle* h)
     return 0;
 }
 
+// recip_div.h's exhaustive host check, once per divisor and process
+static inline bool fl_recip_div_ok(float s)
+{
+    static std::mutex mu;
+    static std::unordered_map<unsigned, bool> seen;
+    unsigned bits; memcpy(&bits, &s, sizeof bits);
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = seen.find(bits);
+    if (it == seen.end()) it = seen.emplace(bits, fl_recip_div_verify(s)).first;
+    return it->second;
+}
+
 static inline int fl_gradient(fluid_handle* h)
 {
     if (int e = fl_rebuild_flags(h)) return e;
@@ -183,14 +197,18 @@ static inline int fl_gradient(fluid_handle* h)
     const float hh = fl_project_h(h), h2 = 2.0f * hh;                       // :330 (2.0f * h)
     unsigned hb; memcpy(&hb, &hh, sizeof hb);
     const unsigned he = (hb >> 23) & 0xffu;
-    static const bool no_pow2 = getenv("FLUID_GRAD_DIV") != nullptr;        // A/B: always divide
-    const bool pow2 = !no_pow2 && (hb & 0x007fffffu) == 0u && he >= 2u && he <= 252u;   // 1/h, 1/(2h) normal and exact
-    if (pow2)
-        k_gradient<true><<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags, h->field[FLUID_VX],
-                                                            h->field[FLUID_VY], h->field[FLUID_VZ], 1.0f / hh, 1.0f / h2);
+    static const bool always_div = getenv("FLUID_GRAD_DIV") != nullptr;     // A/B: always divide
+    const bool pow2 = (hb & 0x007fffffu) == 0u && he >= 2u && he <= 252u;   // 1/h, 1/(2h) normal and exact
+    int mode = FL_GRAD_DIV;
+    if (!always_div) mode = pow2 ? FL_GRAD_POW2 : (fl_recip_div_ok(hh) && fl_recip_div_ok(h2)) ? FL_GRAD_RECIP : FL_GRAD_DIV;
+    const GradScale sc = { hh, h2, 1.0f / hh, 1.0f / h2 };
+    float *vx = h->field[FLUID_VX], *vy = h->field[FLUID_VY], *vz = h->field[FLUID_VZ];
+    if (mode == FL_GRAD_POW2)
+        k_gradient<FL_GRAD_POW2><<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags, vx, vy, vz, sc);
+    else if (mode == FL_GRAD_RECIP)
+        k_gradient<FL_GRAD_RECIP><<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags, vx, vy, vz, sc);
     else
-        k_gradient<false><<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags, h->field[FLUID_VX],
-                                                             h->field[FLUID_VY], h->field[FLUID_VZ], hh, h2);
+        k_gradient<FL_GRAD_DIV><<<q.grid, q.block, 0, h->stream>>>(h->g, h->field[FLUID_PRESSURE], h->cflags, vx, vy, vz, sc);
     FL_CHECK_LAUNCH(h);
     if (h->nranks > 1) {
         float* f[3] = { h->field[FLUID_VX], h->field[FLUID_VY], h->field[FLUID_VZ] };
@@ -238,6 +256,47 @@ static inline int fl_advect(fluid_handle* h, int b, int fid, int pid)     // sim
     if (h->nranks > 1) {
         float* f[1] = { h->field[fid] };
         if (int e = fl_halo_exchange(h, 1, f)) return e;
+    }
+    return 0;
+}
+
+// advect(1, v_x, v_x_prev); advect(2, v_y, v_y_prev); advect(3, v_z, v_z_prev) (simulation.cpp:125-127) as one
+// launch (k_advect3); FLUID_ADVECT_FUSED=0 keeps the three launches (A/B)
+static inline int fl_advect_velocity(fluid_handle* h)
+{
+    static const bool fused_off = getenv("FLUID_ADVECT_FUSED") && atoi(getenv("FLUID_ADVECT_FUSED")) == 0;
+    static const bool quad = getenv("FLUID_ADVECT_QUAD") != nullptr;
+    if (fused_off || quad || h->g.cells >= (1ll << 31)) {
+        if (int e = fl_advect(h, 1, FLUID_VX, FLUID_VX_PREV)) return e;
+        if (int e = fl_advect(h, 2, FLUID_VY, FLUID_VY_PREV)) return e;
+        return fl_advect(h, 3, FLUID_VZ, FLUID_VZ_PREV);
+    }
+    if (int e = fl_rebuild_flags(h)) return e;
+    const int pid[3] = { FLUID_VX_PREV, FLUID_VY_PREV, FLUID_VZ_PREV };
+    GatherSrc3 src;
+    for (int c = 0; c < 3; ++c) {
+        GatherSrc one = {};
+        if (int e = fl_gather_sources(h, pid[c], &one)) return e;
+        for (int r = 0; r < 8; ++r) { src.base[c][r] = one.base[r]; src.zlo[r] = one.zlo[r]; src.dl[r] = one.dl[r]; }
+        src.n = one.n;
+    }
+    if (int e = fl_barrier(h)) return e;          // every rank's slabs of the gather sources are complete
+    static const int ny_env = getenv("FLUID_ADVECT_NY") ? atoi(getenv("FLUID_ADVECT_NY")) : 0;
+    const int NY = (ny_env == 1 || ny_env == 2) ? ny_env : 2;
+    int bx = 32;
+    while (bx < h->g.W && bx < 128) bx <<= 1;
+    const dim3 block(bx, 256 / bx, 1);
+    const dim3 grid((h->g.W + bx - 1) / bx, (h->g.H + block.y * NY - 1) / (block.y * NY), h->g.Dl);
+#define FL_ADV3_LAUNCH(SLAB, N) k_advect3<SLAB, N><<<grid, block, 0, h->stream>>>(h->g, h->field[FLUID_VX], h->field[FLUID_VY], \
+                                    h->field[FLUID_VZ], h->field[FLUID_VX_PREV], h->field[FLUID_VY_PREV], h->field[FLUID_VZ_PREV], \
+                                    src, h->cflags, h->dt)
+    if (src.n > 1) { if (NY == 1) FL_ADV3_LAUNCH(true, 1); else FL_ADV3_LAUNCH(true, 2); }
+    else           { if (NY == 1) FL_ADV3_LAUNCH(false, 1); else FL_ADV3_LAUNCH(false, 2); }
+#undef FL_ADV3_LAUNCH
+    FL_CHECK_LAUNCH(h);
+    if (h->nranks > 1) {
+        float* f[3] = { h->field[FLUID_VX], h->field[FLUID_VY], h->field[FLUID_VZ] };
+        if (int e = fl_halo_exchange(h, 3, f)) return e;
     }
     return 0;
 }
@@ -296,9 +355,7 @@ static inline int fl_step_only(fluid_handle* h)
         if (int e = fl_diffuse(h, batch4 ? 4 : 3, b, f, p)) return e;
     }
     if (int e = fl_project(h)) return e;                                  // :120
-    if (int e = fl_advect(h, 1, FLUID_VX, FLUID_VX_PREV)) return e;       // :125-127, in this order
-    if (int e = fl_advect(h, 2, FLUID_VY, FLUID_VY_PREV)) return e;
-    if (int e = fl_advect(h, 3, FLUID_VZ, FLUID_VZ_PREV)) return e;
+    if (int e = fl_advect_velocity(h)) return e;                          // :125-127, in this order
     if (int e = fl_project(h)) return e;                                  // :130
     if (!(h->flags & FLUID_ELIDE_DEAD) && !batch4) {                      // :135 (dead work, F2)
         const int b = 0, f = FLUID_DENS, p = FLUID_BUFFER;

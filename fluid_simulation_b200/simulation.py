@@ -26,7 +26,7 @@ VOX_HASHED, VOX_FIXED, VOX_CELLS = 0, 1, 2          # fluid_voxelize sampling (i
 ELIDE_DEAD, NO_TILED, TILED_ALWAYS = 0x10, 0x20, 0x40
 
 OP_SET_BOUNDS, OP_LIN_SOLVE, OP_DIFFUSE, OP_DIVERGENCE, OP_GRADIENT = 1, 2, 3, 4, 5
-OP_PROJECT, OP_ADVECT, OP_INFLOW_DENS, OP_INFLOW_VEL, OP_STEP, OP_COPY = 6, 7, 8, 9, 10, 11
+OP_PROJECT, OP_ADVECT, OP_INFLOW_DENS, OP_INFLOW_VEL, OP_STEP, OP_COPY, OP_ADVECT_VEL = 6, 7, 8, 9, 10, 11, 12
 
 FRAME_FILES = ("data.bin", "obs.bin", "v_x.bin", "v_y.bin", "v_z.bin")   # simulation.cpp:56-60
 FRAME_FIELDS = ("dens", "obs", "v_x", "v_y", "v_z")                       # simulation.cpp:143-147
@@ -199,6 +199,7 @@ class Simulation:
     def gradient(self): self._call(OP_GRADIENT)
     def project(self): self._call(OP_PROJECT)
     def advect(self, b, f, prev): self._call(OP_ADVECT, b, f, prev)
+    def advect_velocity(self): self._call(OP_ADVECT_VEL)      # simulation.cpp:125-127, one launch
     def inflow_density(self): self._call(OP_INFLOW_DENS)
     def inflow_velocity(self): self._call(OP_INFLOW_VEL)
 
@@ -263,6 +264,22 @@ class Simulation:
         self._ck(self._L.fluid_streamlines(self._h, C.byref(sp), nl.value, npnt.value, C.byref(nl), C.byref(npnt),
                                            lens.ctypes.data, norm.ctypes.data, pts.ctypes.data))
         return np.split(pts, np.cumsum(lens)[:-1]), norm
+
+    def obstacle_mesh(self, level=0.5) -> dict:
+        """GUI/utils.py:10-38 generate_obstacle_mesh on the resident obstacle field: marching cubes at `level`.
+        Returns the viewer's dict: 'vertexes' (n, 3) float32 in padded [x, y, z] index coordinates, 'faces' (m, 3)
+        int32, 'vertex_colors' (n, 4) opaque grey; empty arrays when there is no obstacle (utils.py:31-37)."""
+        nv, nf = C.c_longlong(0), C.c_longlong(0)
+        self._ck(self._L.fluid_obstacle_mesh(self._h, float(level), 0, 0, C.byref(nv), C.byref(nf), None, None))
+        if nv.value == 0:
+            return {"vertexes": np.array([]), "faces": np.array([]), "vertex_colors": np.array([])}
+        verts = np.zeros((nv.value, 3), np.float32)
+        faces = np.zeros((max(nf.value, 1), 3), np.int32)
+        self._ck(self._L.fluid_obstacle_mesh(self._h, float(level), nv.value, faces.shape[0], C.byref(nv), C.byref(nf),
+                                             verts.ctypes.data, faces.ctypes.data))
+        colors = np.ones((nv.value, 4))
+        colors[:, :3] = 0.5                                       # utils.py:20-24
+        return {"vertexes": verts, "faces": faces[:nf.value], "vertex_colors": colors}
 
     def launch_count(self) -> int:
         return int(self._L.fluid_launch_count(self._h))

@@ -63,7 +63,8 @@ enum fluid_op {
     FLUID_OP_INFLOW_DENS = 8,  /* addDensity(1,j,k,0.001f) on the x=1 face  simulation.cpp:65-67 */
     FLUID_OP_INFLOW_VEL  = 9,  /* setVelocity(1,j,k,speed,0,0) on x=1 face  simulation.cpp:103-105 */
     FLUID_OP_STEP        = 10, /* Simulation::step() without run()'s prologue simulation.cpp:96-138 */
-    FLUID_OP_COPY        = 11  /* field = prev (buffer = dens, v_prev = v)    simulation.cpp:70, 108-110 */
+    FLUID_OP_COPY        = 11, /* field = prev (buffer = dens, v_prev = v)    simulation.cpp:70, 108-110 */
+    FLUID_OP_ADVECT_VEL  = 12  /* advect(1,v_x,..); advect(2,v_y,..); advect(3,v_z,..) as step() runs them  simulation.cpp:125-127 */
 };
 
 enum fluid_error {
@@ -192,6 +193,18 @@ typedef struct fluid_streamline_params {
 } fluid_streamline_params;
 int fluid_streamlines(fluid_handle*, const fluid_streamline_params* params, int max_lines, long long max_points,
                       int* n_lines, long long* n_points, int* line_len, double* norm_speed, double* points);
+
+/* GUI/utils.py:10-38 (generate_obstacle_mesh): marching cubes of the padded obstacle volume at `level` (the viewer:
+ * 0.5), vertices in padded (x, y, z) index coordinates as main_window.py:204 hands the volume over.  One vertex per
+ * grid edge whose ends lie on different sides of the level (linear interpolation: the midpoint for a 0/1 volume),
+ * faces as vertex-index triples with normals towards lower values (skimage's gradient_direction='descent').
+ * *n_verts / *n_faces always receive the counts.  verts == faces == NULL: sizing query, returns 0.  Otherwise
+ * verts (3 floats per vertex) and faces (3 ints per face) are filled when the counts fit max_verts / max_faces,
+ * else nothing is copied and the call fails with FLUID_E_ARG.  No obstacle: 0 vertices, 0 faces (the viewer's
+ * empty mesh).  The face list and the vertex order are this library's own: skimage's Lewiner variant is not
+ * available here to pin them against. */
+int fluid_obstacle_mesh(fluid_handle*, double level, long long max_verts, long long max_faces, long long* n_verts,
+                        long long* n_faces, float* verts, int* faces);
 
 int fluid_sync(fluid_handle*);
 const char* fluid_last_error(fluid_handle*);

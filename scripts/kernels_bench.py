@@ -21,6 +21,7 @@ def main():
     cells = a.w * a.h * a.d
     ops = [("divergence", 20, lambda: sim.divergence()), ("gradient", 28, lambda: sim.gradient()),
            ("advect v_x", 16, lambda: sim.advect(1, "v_x", "v_x_prev")), ("advect v_z", 16, lambda: sim.advect(3, "v_z", "v_z_prev")),
+           ("advect v_x+v_y+v_z (one launch)", 32, lambda: sim.advect_velocity()),
            ("advect dens", 20, lambda: sim.advect(0, "dens", "buffer")), ("setBounds", 8, lambda: sim.setBounds(1, "v_x")),
            ("copy", 8, lambda: sim._call(OP_COPY, 0, "buffer", "dens")), ("stats", 16, lambda: sim.stats())]
     out = {}
@@ -30,7 +31,7 @@ def main():
         for _ in range(a.reps): fn()
         us = sim.timer_stop() * 1e3 / a.reps
         out[name] = {"us": round(us, 1), "GBps": round(bpc * cells / us / 1e3, 1), "frac": round(bpc * cells / us / 1e3 / peak, 3)}
-        print(f"{name:12s} {us:8.1f} us  {bpc:2d} B/cell  {bpc * cells / us / 1e3:7.1f} GB/s  {bpc * cells / us / 1e3 / peak:5.2f} of measured peak")
+        print(f"{name:32s} {us:8.1f} us  {bpc:2d} B/cell  {bpc * cells / us / 1e3:7.1f} GB/s  {bpc * cells / us / 1e3 / peak:5.2f} of measured peak")
     print(json.dumps({"kernels": out, "cfg": vars(a)}))
     sim.close()
 

@@ -58,8 +58,9 @@ def test_hot_path_kernels_are_fma_free_and_use_tma():
                     per[name][k] += 1
     hot = [n for n in per if re.search(r"k_sweep_|k_divergence|k_advect|k_inflow|k_set_bounds|k_copy_edges|k_lex_|k_pack|k_unpack|k_build", n)]
     assert hot and all(per[n]["FFMA"] == 0 for n in hot), {n: per[n]["FFMA"] for n in hot if per[n]["FFMA"]}
-    # k_gradient<false> divides by h / 2h (IEEE division sequences contain FFMA by construction); the
-    # power-of-two form the benchmark grids take multiplies and must be clean
+    # k_gradient<FL_GRAD_DIV> divides by h / 2h (IEEE division sequences contain FFMA by construction) and
+    # <FL_GRAD_RECIP> holds the two explicit FMAs of csrc/recip_div.h's quotient; the power-of-two form the
+    # benchmark grids take multiplies and must be clean
     grad = [n for n in per if "k_gradient" in n]
     assert any(per[n]["FFMA"] == 0 for n in grad), {n: per[n]["FFMA"] for n in grad}
     sweeps = [n for n in per if "k_sweep_stream" in n or "k_sweep_pair" in n]

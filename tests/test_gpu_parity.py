@@ -56,6 +56,24 @@ def test_advect(w, h, d, b):
     check(gpu, cpu, f"advect b={b}")
 
 
+@pytest.mark.parametrize("w,h,d", SIZES + [(130, 70, 9), (256, 40, 6)])
+@pytest.mark.parametrize("obstacle", [False, True])
+def test_advect_velocity_fused(w, h, d, obstacle):
+    """step()'s three velocity advections (simulation.cpp:125-127) as ONE launch against the three calls on the
+    CPU: each reads what the previous one (and its setBounds) left at its own cell."""
+    gpu, cpu = make_pair(w, h, d, 4, 0, ORDER_RB)
+    if obstacle:
+        from fluid_simulation_b200 import masks
+        obs = masks.sphere(w, h, d)
+        gpu.set("obs", obs); cpu.set("obs", obs)
+    for n in ("v_x", "v_y", "v_z", "v_x_prev", "v_y_prev", "v_z_prev"):
+        a = cpu.get(n) * 30.0
+        gpu.set(n, a); cpu.set(n, a)
+    gpu.advect_velocity()
+    cpu.advect(1, "v_x", "v_x_prev"); cpu.advect(2, "v_y", "v_y_prev"); cpu.advect(3, "v_z", "v_z_prev")
+    check(gpu, cpu, "fused velocity advection")
+
+
 @pytest.mark.parametrize("w,h,d", SIZES)
 def test_divergence_and_gradient(w, h, d):
     gpu, cpu = make_pair(w, h, d, 4, 0, ORDER_RB)
@@ -68,12 +86,15 @@ def test_divergence_and_gradient(w, h, d):
     check(gpu, cpu, "gradient")
 
 
-@pytest.mark.parametrize("w,h,d", [(16, 16, 16), (64, 32, 16), (32, 8, 2), (16, 16, 8)])
+@pytest.mark.parametrize("w,h,d", [(16, 16, 16), (64, 32, 16), (32, 8, 2), (16, 16, 8), (16, 8, 8), (64, 64, 128),
+                                   (24, 16, 12), (100, 10, 10)])
 def test_gradient_extreme_pressures(w, h, d):
     """Where h = 1/cbrtf(W*H*D) is a power of two (the first three shapes) k_gradient multiplies by 1/h
     instead of dividing by h; the claim is that this is exact for EVERY float, so the pressure field holds
     zeros of both signs, denormals, the smallest / largest normals and values whose differences overflow.
-    (16, 16, 8) has a non-power-of-two h and takes the dividing kernel on the same data.)"""
+    The other shapes have a non-power-of-two h: the kernel multiplies by the rounded reciprocal and corrects with
+    one FMA (csrc/recip_div.h) inside [2^-60, 2^60] and divides outside.  (16, 8, 8) and (64, 64, 128) have the
+    significand of h that 256 x 256 x 512 and 1024 x 512 x 512 have (W*H*D = 2^(3k+1): h = 2^-k / cbrt(2)).)"""
     gpu, cpu = make_pair(w, h, d, 4, 0, ORDER_RB)
     rng = np.random.default_rng(w * 131 + d)
     shape = cpu.shape
