@@ -34,6 +34,9 @@ def lib():
         L.oracle_render_slice.restype = None
         L.oracle_render_slice.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
                                           C.c_void_p, C.c_void_p]
+        L.mo_marching_cubes.restype = C.c_int
+        L.mo_marching_cubes.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.POINTER(C.c_longlong),
+                                        C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -81,3 +84,17 @@ def render_slice(field, obs, z, vmin, vmax, alpha=0.2) -> np.ndarray:
     lib().oracle_render_slice(f.ctypes.data, o.ctypes.data, f.shape[1], f.shape[0], float(vmin), float(vmax), float(alpha),
                               lut.ctypes.data, out.ctypes.data)
     return out
+
+
+def marching_cubes(obs, level=0.5):
+    """oracle/mesh_oracle.c on a padded obstacle frame (nz, ny, nx): (verts (n, 3) float32 in [x, y, z] index
+    coordinates, faces (m, 3) int32) -- what GUI/utils.py:17 asks skimage for (parity unpinned, see the C file)."""
+    a = np.ascontiguousarray(obs, dtype=np.float32)
+    nz, ny, nx = a.shape
+    nv, nf = C.c_longlong(0), C.c_longlong(0)
+    ptr = a.ctypes.data
+    assert lib().mo_marching_cubes(ptr, nx, ny, nz, level, C.byref(nv), C.byref(nf), None, None) == 0
+    verts = np.zeros((nv.value, 3), np.float32)
+    faces = np.zeros((nf.value, 3), np.int32)
+    assert lib().mo_marching_cubes(ptr, nx, ny, nz, level, C.byref(nv), C.byref(nf), verts.ctypes.data, faces.ctypes.data) == 0
+    return verts, faces
