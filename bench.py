@@ -227,6 +227,10 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from fluid_simulation_b200 import Simulation, masks, SOLVER_RB, SOLVER_JACOBI, ELIDE_DEAD, _lib
     from fluid_simulation_b200 import slab as slabmod
+    bound = None
+    if world > 1:                       # node-local pinned frame buffers: each rank next to its own GPU
+        from fluid_simulation_b200 import multi_gpu
+        bound = multi_gpu.bind_host_to_gpu(local)
 
     w, h, d, acc = workload(world, args)
     flags = {"rb": SOLVER_RB, "jacobi": SOLVER_JACOBI}[args.solver] | (ELIDE_DEAD if args.elide else 0)
@@ -328,7 +332,9 @@ def run_ours(args):
                                       if (w, h, acc, args.strong) == (W0, H0, ACC0, False) else "(custom size)"),
                        "solver": args.solver, "density_diffusion": "elided" if args.elide else "executed",
                        "parallelism": f"z-slab x{world}" if world > 1 else "1 GPU",
-                       "l2": "state (11 fields, %.0f MB) exceeds the 126 MB L2" % (11 * 4 * local_cells / 1e6)},
+                       "l2": "state (11 fields, %.0f MB) exceeds the 126 MB L2" % (11 * 4 * local_cells / 1e6),
+                       "host_affinity": (f"each rank pinned to the {len(bound)} CPUs NVML lists for its GPU" if bound
+                                         else "unchanged")},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
             "cpu_baseline": cpu, "slab_parity": slab_parity, "extra": extra,
             "stats": {k: float(v) for k, v in stats.items()},

@@ -161,6 +161,8 @@ static inline float* fl_peer_ptr(fluid_handle* h, int r, const float* local)
     return nullptr;
 }
 
+bool fl_peer_mapped(fluid_handle* h, int r, const float* local) { return fl_peer_ptr(h, r, local) != nullptr; }
+
 // every buffer a sweep can write and the flag block are mapped from both z-neighbours, and the
 // driver offers stream waits on memory: sweeps hand their halos over by peer stores
 static inline bool fl_push_ready(fluid_handle* h);

@@ -27,6 +27,7 @@ bool fl_push_usable(fluid_handle* h);
 int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stream, unsigned seq, int nplanes = 2);
 int fl_halo_wait(fluid_handle* h, cudaStream_t stream, unsigned seq);
 int fl_push_targets(fluid_handle* h, int n, float* const* fields, float* (*peer)[4], unsigned** flag, int* zdst);
+bool fl_peer_mapped(fluid_handle* h, int r, const float* local);            // comm.cuh: rank r's copy of this buffer is IPC-mapped
 int fl_barrier(fluid_handle* h);                                         // comm.cuh
 
 static inline int fl_rebuild_flags(fluid_handle* h)

@@ -58,6 +58,7 @@ struct alignas(64) StreamArgs {
     const unsigned* my_flag;             // this rank's arrival flags [face]; an edge segment starts once its face shows seq - 1
     unsigned* err_word;                  // set when an arrival flag did not show up within SW_ARRIVAL_TIMEOUT_NS
     int dbg;                             // FLUID_SW_DBG timing experiments: 1 = no stores, 2 = no relaxation (results invalid)
+    unsigned long long* trace;           // FLUID_SW_TRACE: per CTA { start, first segment done, end } in globaltimer ns; else nullptr
 };
 
 // ---- PTX wrappers (mbarrier + TMA) -----------------------------------------------------------
@@ -484,12 +485,19 @@ __device__ __forceinline__ void sw_segment(const StreamArgs& A, const SwSeg sg, 
     // A face segment streams away from its slab face: after four steps the two boundary planes are final
     // and go to the z-neighbour while the rest of the segment is still being swept.
     const int face = (sg.mode >> 1) - 1;
-#define SW_HAND_OVER if (face >= 0 && step == 4 && !(A.dbg & 8)) sw_push_face<GE::TY, GE::THREADS>(A, g, out, batch, sg.col - bx * A.nty, y0, xtile == 0 ? 0 : (FL_XOFF + own_lo) / 4, xtile == A.nxt - 1 ? g.pitch / 4 : (FL_XOFF + own_hi + 1) / 4, face, tid);
+    // Four steps later the stores are long on their way: fence them and count this CTA in (the last one raises the
+    // neighbour's flag) -- early in the segment, however long it is, so that the neighbour's next sweep never waits
+    // for the end of this one (dbg 16: only when the segment is done, as before).
+    bool signalled = false;
+#define SW_HAND_OVER if (face >= 0 && !(A.dbg & 8)) {                                                                                  \
+        if (step == 4) sw_push_face<GE::TY, GE::THREADS>(A, g, out, batch, sg.col - bx * A.nty, y0, xtile == 0 ? 0 : (FL_XOFF + own_lo) / 4,  \
+                                                         xtile == A.nxt - 1 ? g.pitch / 4 : (FL_XOFF + own_hi + 1) / 4, face, tid);         \
+        else if (step == 8 && !(A.dbg & 16)) { sw_signal_face(A, face, tid); signalled = true; } }
     if (((g.zlo + ps) & 1) == 0) { for (;;) { SW_HAND_OVER SW_STEP(0, 0) SW_STEP(1, 1) SW_STEP(2, 0) SW_STEP(3, 1) } }
     else                         { for (;;) { SW_HAND_OVER SW_STEP(0, 1) SW_STEP(1, 0) SW_STEP(2, 1) SW_STEP(3, 0) } }
 #undef SW_STEP
 #undef SW_HAND_OVER
-    if (face >= 0 && !(A.dbg & 8)) sw_signal_face(A, face, tid);
+    if (face >= 0 && !(A.dbg & 8) && !signalled) sw_signal_face(A, face, tid);
 }
 
 // MODE 0 = Jacobi, 1 = red-black (colour 0 = (x+y+z) even first).  A CTA works through a short list
@@ -523,6 +531,7 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     __syncthreads();
+    if (A.trace && tid == 0) { unsigned long long tt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt)); A.trace[4 * blockIdx.x] = tt; }
 
     // what is constant for the thread across segments
     SwThread t;
@@ -549,7 +558,12 @@ __global__ void __launch_bounds__(32 * TXW * NP, CPS) k_sweep_stream(const __gri
             sw_segment<TXW, NP, CPS, MODE, -1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, qx, safe);
         else
             sw_segment<TXW, NP, CPS, MODE, 1>(A, sg, t, uring, vbuf, bars, s_iss, s_con, ph_con, tid, pr, rA, qx, safe);
+        if (A.trace && tid == 0 && si == A.seg_first[blockIdx.x]) {
+            unsigned long long tt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+            A.trace[4 * blockIdx.x + 1] = tt; A.trace[4 * blockIdx.x + 3] = (unsigned long long)(unsigned)sg.mode | ((unsigned long long)(sg.zb - sg.za + 1) << 8);
+        }
     }
+    if (A.trace && tid == 0) { unsigned long long tt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt)); A.trace[4 * blockIdx.x + 2] = tt; }
     if (A.nty < 0) A.dst[0][0] = __uint_as_float(t.sink);            // never taken: keeps t.sink observable
 }
 
@@ -571,8 +585,10 @@ struct StreamState {
     int zc_override = 0;
     bool zigzag = true, unbatch = false, overlap = true;
     int cfg = 0, dbg = 0;
-    bool face_cta = true;                                       // separate edge CTAs (plan part 4); FLUID_SW_FACE_CTA=0: hand-over inside ordinary segments (part 5)
+    int face_mode = 2;                                          // FLUID_SW_FACE_CTA: 2 = edge segments first in the CTAs that would otherwise start behind them (plan part 6, one wave), 1 = separate edge CTAs (part 4), 0 = hand-over inside ordinary segments (part 5)
     int edge = SW_EDGE_DEFAULT;                                 // planes per edge segment at an interior slab face (>= 2)
+    unsigned long long* trace = nullptr; const char* trace_path = nullptr; long trace_launch = 0, trace_at[2] = { -1, -1 };   // FLUID_SW_TRACE=path, FLUID_SW_TRACE_AT=i,j
+    int late_extra = -1;                                        // FLUID_SW_LATE: extra pipeline steps the plan charges a CTA that starts behind an edge CTA
     int plan_mode = 2, plan_min_fill = 85;
     // zero-bit volume (k_build_zbits): rebuilt whenever the flag volume was
     unsigned short* zbits[2] = { nullptr, nullptr }; int zb_pairs = 0, zb_lanes = 0; unsigned long long zb_version = ~0ull;
@@ -595,7 +611,13 @@ inline StreamState* sw_state(fluid_handle* h)
         if (const char* e = getenv("FLUID_SW_CFG")) s->cfg = atoi(e);
         if (const char* e = getenv("FLUID_SW_DBG")) s->dbg = atoi(e);
         if (const char* e = getenv("FLUID_SW_EDGE")) { s->edge = atoi(e); if (s->edge < 2) s->edge = 2; }
-        if (const char* e = getenv("FLUID_SW_FACE_CTA")) s->face_cta = atoi(e) != 0;
+        if (const char* e = getenv("FLUID_SW_FACE_CTA")) s->face_mode = atoi(e);
+        if (const char* e = getenv("FLUID_SW_LATE")) s->late_extra = atoi(e);
+        if (const char* e = getenv("FLUID_SW_TRACE")) {
+            s->trace_path = e;
+            if (cudaMalloc(&s->trace, 4096 * 4 * sizeof(unsigned long long)) != cudaSuccess) s->trace = nullptr;
+            if (const char* at = getenv("FLUID_SW_TRACE_AT")) sscanf(at, "%ld,%ld", &s->trace_at[0], &s->trace_at[1]);
+        }
         if (const char* e = getenv("FLUID_SW_PLAN")) s->plan_mode = atoi(e);
         if (const char* e = getenv("FLUID_SW_PLAN_FILL")) s->plan_min_fill = atoi(e);
         if (const char* e = getenv("FLUID_SW_PDL")) s->pdl = atoi(e);
@@ -611,7 +633,7 @@ inline void fl_tiled_release(fluid_handle* h)
 {
     StreamState* s = (StreamState*)h->tiled;
     if (s) for (auto& kv : s->plans) { cudaFree(kv.second.segs); cudaFree(kv.second.seg_first); }
-    if (s) { cudaFree(s->zbits[0]); cudaFree(s->zbits[1]); }
+    if (s) { cudaFree(s->zbits[0]); cudaFree(s->zbits[1]); cudaFree(s->trace); }
     delete s;
     h->tiled = nullptr;
 }
@@ -704,28 +726,38 @@ inline int sw_get_map(fluid_handle* h, const float* buf, int box_w, int box_rows
 // planes in between on all SMs (halos handed over by peer stores: nothing else needs an SM), where the
 // CTAs that only start once an edge CTA has retired get that much less work; part 4 = parts 1 and 3 in
 // one grid, edge CTAs first, for the sweep that hands its halos over itself; part 5 = all planes as in
-// part 0, the segments that touch a slab face doing the hand-over on their way (FLUID_SW_FACE_CTA=0; as fast
-// with one face per rank, slower with two: 4 GPUs 30.2 vs 27.9 ms/step).
+// part 0, the segments that touch a slab face doing the hand-over on their way (FLUID_SW_FACE_CTA=0; slower with
+// two faces: 4 GPUs 24.9 vs 24.1 ms/step); part 6 = part 4 in ONE wave: the edge segment is the first segment of
+// the CTA that part 4 would start behind it, so no CTA retires and none is dispatched mid-sweep (the default:
+// 22.6 vs 22.8 ms on 2 GPUs, 23.2 vs 23.4 on 4).
+inline std::pair<int, int> sw_plan_key(int nb, int ty, int cps, int part, int segcost) { return std::make_pair(nb, ((ty * 16 + cps) * 8 + part) * 16 + segcost); }
+
 inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPlan* out, int segcost = SW_SEGCOST)
 {
     StreamState* s = sw_state(h);
-    auto key = std::make_pair(nb, ((ty * 16 + cps) * 8 + part) * 16 + segcost);
+    auto key = sw_plan_key(nb, ty, cps, part, segcost);
     auto it = s->plans.find(key);
     if (it == s->plans.end()) {
         const Grid& g = h->g;
         const bool lo_face = h->rank > 0, hi_face = h->rank < h->nranks - 1;
         // planes zoff+1 .. zoff+Dl of every column are distributed (part 0: zoff = 0, Dl = g.Dl)
-        const bool split = part >= 2 && part <= 4;          // edge planes have CTAs of their own
+        const bool split = (part >= 2 && part <= 4) || part == 6;   // edge planes have segments of their own
         const int zoff = (split && lo_face) ? s->edge : 0;
         const int Dl = split ? g.Dl - zoff - (hi_face ? s->edge : 0) : g.Dl;
         const int nty = (g.H + ty - 1) / ty, ncol = nb * nty;
         const long long T = (long long)ncol * Dl;
         std::vector<SwSeg> segs; std::vector<int> first;
-        if (part == 1 || part == 4) {
+        std::vector<SwSeg> edge_segs;                       // part 6: kept aside, merged below
+        if (part == 1 || part == 4 || part == 6) {
             // part 4: the edge CTAs come first in the grid (they are dispatched first) and hand their
             // boundary planes to the z-neighbour themselves; they stream away from the face
-            const int lo_mode = part == 4 ? (1 << 1) : 0, hi_mode = part == 4 ? (2 << 1) | 1 : 0;
+            const int lo_mode = part != 1 ? (1 << 1) : 0, hi_mode = part != 1 ? (2 << 1) | 1 : 0;
             for (int c = 0; c < ncol; ++c) {
+                if (part == 6) {
+                    if (lo_face) edge_segs.push_back(SwSeg{ c, 1, s->edge, lo_mode });
+                    if (hi_face) edge_segs.push_back(SwSeg{ c, g.Dl - s->edge + 1, g.Dl, hi_mode });
+                    continue;
+                }
                 if (lo_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, 1, s->edge, lo_mode }); }
                 if (hi_face) { first.push_back((int)segs.size()); segs.push_back(SwSeg{ c, g.Dl - s->edge + 1, g.Dl, hi_mode }); }
             }
@@ -751,8 +783,10 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
             // slot frees up, so the last n_edge % nc of them start one edge segment (+ its pipeline fill) later
             // than the others and get that much less work
             const long long n_edge = (long long)ncol * ((lo_face ? 1 : 0) + (hi_face ? 1 : 0));
-            const long long n_prompt = (part == 3 || part == 4) ? nc - n_edge % nc : nc;
-            const long long late = s->edge + segcost + 2;
+            const long long n_prompt = (part == 3 || part == 4 || part == 6) ? nc - n_edge % nc : nc;
+            // measured (4 GPUs, 256^3 per rank): a rank with two faces gains 2.8 % when a late CTA is charged 4 steps more,
+            // a rank with one face loses as much (2 GPUs) -- FLUID_SW_LATE overrides
+            const long long late = s->edge + segcost + 2 + (s->late_extra >= 0 ? s->late_extra : (lo_face && hi_face) ? 4 : 0);
             // Uniform plan: every column is cut into the same S ranges and one CTA streams range k of a
             // column, upwards for even k, downwards for odd k.  Neighbouring row tiles are then on the same
             // plane at the same time and the ranges of a column reach their shared boundary together, so
@@ -799,6 +833,22 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
             }
         }
         first.push_back((int)segs.size());
+        if (part == 6) {
+            // One wave: the CTA that part 4 starts behind edge CTA k sweeps that edge segment itself, first, and goes
+            // on with its (shorter) share of the planes in between -- no CTA retires and none is dispatched mid-sweep.
+            const long long nc_built = (long long)first.size() - 1;
+            const long long n_e = (long long)edge_segs.size();
+            if (s->zc_override > 0 || n_e > nc_built) return sw_get_plan(h, nb, ty, cps, 4, out, segcost);
+            std::vector<SwSeg> s2; std::vector<int> f2;
+            for (long long k = 0; k < nc_built; ++k) {
+                f2.push_back((int)s2.size());
+                const long long e = k - (nc_built - n_e);
+                if (e >= 0) s2.push_back(edge_segs[(size_t)e]);
+                s2.insert(s2.end(), segs.begin() + first[(size_t)k], segs.begin() + first[(size_t)k + 1]);
+            }
+            f2.push_back((int)s2.size());
+            segs.swap(s2); first.swap(f2);
+        }
         if (part == 5) {
             // Hand-over inside ordinary segments: the first segment of a column (za = 1) takes the lower face,
             // the last (zb = Dl) the upper face; a segment that spans a whole column with two faces is cut
@@ -880,7 +930,8 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     if (nq > qmax) { nxt = (nq - 2 + (qmax - 2) - 1) / (qmax - 2); xq = (nq + nxt - 1) / nxt; }
     const int nbx = nb * nxt;
     SwPlan plan, plan_edge;
-    if (int e = sw_get_plan(h, nbx, GE::TY, CPS, fused ? (s->face_cta ? 4 : 5) : overlap ? 2 : 0, &plan)) return e;
+    const int plan_part = fused ? (s->face_mode == 2 ? 6 : s->face_mode == 1 ? 4 : 5) : overlap ? 2 : 0;
+    if (int e = sw_get_plan(h, nbx, GE::TY, CPS, plan_part, &plan)) return e;
     if (overlap && !fused) if (int e = sw_get_plan(h, nbx, GE::TY, CPS, 1, &plan_edge)) return e;
     StreamArgs A;
     A.g = g; A.a = a; A.c_recip = 1.0f / c;                              // simulation.cpp:257
@@ -889,7 +940,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     A.nty = (g.H + GE::TY - 1) / GE::TY;
     A.nxt = nxt; A.xt_cells = 4 * xq;
     A.segs = plan.segs; A.seg_first = plan.seg_first;
-    A.dbg = s->dbg;
+    A.dbg = s->dbg; A.trace = nullptr;
 
     float* cur[4]; float* alt[4];
     if (nb > 4) return fl_fail(h, FLUID_E_ARG, "streaming solve: %d batched fields", nb);
@@ -939,9 +990,12 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         }
         A.flip = (s->zigzag && ((k + first_sweep) & 1)) ? 1 : 0;         // odd sweeps stream the other way (L2 reuse)
         const sweep_kernel kern = kerns[mixed ? 2 : A.flip];
+        const bool tracing = s->trace && s->trace_path && plan.nctas <= 4096 && (s->trace_launch == s->trace_at[0] || s->trace_launch == s->trace_at[1]);
+        A.trace = tracing ? s->trace : nullptr;
+        ++s->trace_launch;
         const unsigned seq = push ? ++h->halo_seq : 0u;
         if (fused) {
-            if (int e = fl_push_targets(h, nb, alt, A.peer_dst, A.peer_flag, A.peer_zdst)) return e;
+            if (int e = fl_push_targets(h, nb, A.dst, A.peer_dst, A.peer_flag, A.peer_zdst)) return e;   // the buffers this sweep writes
             A.counter = h->d_sync + 2; A.n_edge = nbx * A.nty; A.seq = seq;
             A.my_flag = h->d_sync; A.err_word = h->d_sync + 16;
         } else if (overlap) {
@@ -963,6 +1017,20 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
         } else
             kern<<<plan.nctas, GE::THREADS, GE::SMEM, h->stream>>>(A);
         FL_CHECK_LAUNCH(h);
+        if (tracing) {                                                     // diagnostic: per-CTA timeline of this launch
+            std::vector<unsigned long long> tr((size_t)plan.nctas * 4);
+            FL_CUDA(h, cudaStreamSynchronize(h->stream));
+            FL_CUDA(h, cudaMemcpy(tr.data(), s->trace, tr.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+            char path[512]; snprintf(path, sizeof path, "%s.r%d.l%ld.txt", s->trace_path, h->rank, s->trace_launch - 1);
+            if (FILE* f = fopen(path, "w")) {
+                unsigned long long t0 = ~0ull;
+                for (int k = 0; k < plan.nctas; ++k) if (tr[4 * k] < t0) t0 = tr[4 * k];
+                fprintf(f, "# rank %d launch %ld fields %d ctas %d: cta start_ns first_segment_done_ns end_ns first_mode first_planes\n", h->rank, s->trace_launch - 1, nb, plan.nctas);
+                for (int k = 0; k < plan.nctas; ++k)
+                    fprintf(f, "%d %llu %llu %llu %llu %llu\n", k, tr[4 * k] - t0, tr[4 * k + 1] - t0, tr[4 * k + 2] - t0, tr[4 * k + 3] & 0xffull, tr[4 * k + 3] >> 8);
+                fclose(f);
+            }
+        }
         for (int i = 0; i < nb; ++i) if (!((from_rhs >> i) & 1u)) { float* t = cur[i]; cur[i] = alt[i]; alt[i] = t; }
         if (fused) {
             // the next sweep's edge CTAs wait for the neighbours' halos themselves (sw_await_face);
@@ -1007,7 +1075,18 @@ inline bool fl_tiled_eligible(fluid_handle* h)
 inline bool fl_swap_instead_of_copy(fluid_handle* h)
 {
     static const bool off = getenv("FLUID_NO_SWAP") != nullptr;
-    if (off || h->nranks != 1 || h->acc <= 0 || !fl_tiled_eligible(h)) return false;
+    static const bool slab_off = getenv("FLUID_NO_SLAB_SWAP") != nullptr;
+    if (off || h->acc <= 0 || !fl_tiled_eligible(h)) return false;
+    // z-slabs: every rank swaps the same way, and the peers' mappings are looked up by allocation, so the
+    // hand-over follows the buffers; only on the path where the sweeps push their halos themselves
+    if (h->nranks > 1) {
+        if (slab_off || !fl_push_usable(h)) return false;
+        // advect() gathers from every rank's *_prev buffers, which after a swap are the allocations that held v:
+        // both sets must be mapped from everybody (hosts that map only the original gather sources keep the copies)
+        for (int r = 0; r < h->nranks; ++r)
+            for (int k = 0; k < 3 && r != h->rank; ++k)
+                if (!fl_peer_mapped(h, r, h->field[FLUID_VX + k]) || !fl_peer_mapped(h, r, h->field[FLUID_VX_PREV + k])) return false;
+    }
     StreamState* s = sw_state(h);
     return s->encode != nullptr && !s->unbatch;
 }
@@ -1054,6 +1133,7 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
         else if (s->cfg == 1 && g.W <= 256) e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         else if (s->cfg == 2 && g.W <= 256) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         else if (s->cfg == 3 && g.W <= 256) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
+        else if (s->cfg == 4 && g.W <= 256) e = sw_run<2, 9, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);   // 16 owned rows: 16 tiles at H = 256 instead of 19
         else if (g.W > 256 && g.W <= 512 && s->cfg != 5) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         if (e) return e;

@@ -47,7 +47,8 @@ Simulation::Simulation(slab::Hub& hub, int w, int h, int d, int iter_, int speed
     std::vector<char> mine(per), all(per * nranks_);
     for (int a = 0; a < FLUID_IPC_COUNT; ++a) check(fluid_ipc_export(h_, a, mine.data() + 64 * a), "ipc_export");
     hub.allgather(mine.data(), per, all.data());
-    static const int gather_ids[5] = { FLUID_VX_PREV, FLUID_VY_PREV, FLUID_VZ_PREV, FLUID_BUFFER, FLUID_IPC_SYNC };
+    // (v_x, v_y, v_z too: step() trades them with the *_prev buffers instead of copying, so they are gather sources every other step)
+    static const int gather_ids[8] = { FLUID_VX_PREV, FLUID_VY_PREV, FLUID_VZ_PREV, FLUID_BUFFER, FLUID_VX, FLUID_VY, FLUID_VZ, FLUID_IPC_SYNC };
     for (int r = 0; r < nranks_; ++r) {
         if (r == rank_) continue;
         const char* hr = all.data() + per * r;

@@ -15,6 +15,9 @@ from .simulation import FIELDS, FluidError
 
 # the fields advect() gathers from: prev_field of each of the four calls (simulation.cpp:125-127, 136)
 GATHER_SOURCES = ("v_x_prev", "v_y_prev", "v_z_prev", "buffer")
+# step() trades v and v_prev instead of copying (simulation.cpp:108-110), so the allocations behind v_x, v_y, v_z are
+# gather sources every other step: mapped from every rank as well (without them the library keeps the copies)
+GATHER_PARTNERS = ("v_x", "v_y", "v_z")
 IPC_COUNT = len(FIELDS) + 5            # fields, 4 solver ping-pong partners, flag block (FLUID_IPC_COUNT)
 IPC_SYNC = len(FIELDS) + 4             # FLUID_IPC_SYNC: arrival flags of the z-neighbours, barrier epochs of every rank
 
@@ -29,6 +32,34 @@ def nccl_library_path() -> str:
     except Exception:
         pass
     return "libnccl.so.2"
+
+
+def bind_host_to_gpu(local_rank: int):
+    """Pin this process to the CPUs NVML names as closest to its GPU (same NUMA node, same PCIe root), so that
+    the pinned frame buffers it allocates afterwards are node-local (first touch) and eight ranks dumping at once
+    do not all write through one socket.  Returns the CPU list, or None when NVML or the call is unavailable
+    (nothing is changed then).  FLUID_NO_BIND=1 switches it off (A/B)."""
+    if os.environ.get("FLUID_NO_BIND"):
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        index = local_rank                                   # NVML counts physical devices
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",")
+        if all(v.strip().isdigit() for v in visible) and local_rank < len(visible):
+            index = int(visible[local_rank])
+        handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (ncpu + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = sorted(c for c in cpus if c in allowed)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
 
 
 def broadcast_bytes(dist, payload: bytes | None, n: int, src: int = 0) -> bytes:
@@ -67,7 +98,7 @@ def attach(sim, dist, lib=None) -> None:
     sim._ck(L.fluid_comm_init(sim._h, path, uid))
     # CUDA IPC: the advection gather sources of every rank, and every solver buffer + the arrival flags of
     # the two z-neighbours (sweeps then hand their halo planes over by peer stores, see include/fluid_cuda.h)
-    gather_ids = [FIELDS[name] for name in GATHER_SOURCES]
+    gather_ids = [FIELDS[name] for name in GATHER_SOURCES + GATHER_PARTNERS]
     mine = {}
     for aid in range(IPC_COUNT):
         buf = C.create_string_buffer(64)

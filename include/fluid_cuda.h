@@ -242,7 +242,9 @@ int fluid_comm_unique_id(const char* nccl_lib_path, char out[128]);
 int fluid_comm_init(fluid_handle*, const char* nccl_lib_path, const char unique_id[128]);
 /* advect() gathers at arbitrary z (simulation.cpp:384-397): the gather sources v_x_prev, v_y_prev,
  * v_z_prev and buffer of every other rank are mapped through CUDA IPC (64-byte handles, exchanged by
- * the host program) and read over NVLink by the advection kernel.
+ * the host program) and read over NVLink by the advection kernel.  Map v_x, v_y, v_z of every other rank as
+ * well: step() then trades v and v_prev instead of copying (simulation.cpp:108-110), which makes those
+ * allocations gather sources every other step; without them the three copies stay.
  * The linearSolver sweeps (simulation.cpp:258-272) hand their halo planes to the z-neighbours the same
  * way once the neighbours' allocations are mapped: ids 0..FLUID_NFIELDS-1 are the fields,
  * FLUID_IPC_SCRATCH0..+3 the solver's ping-pong partners and FLUID_IPC_SYNC the flag block (arrival flags

@@ -119,6 +119,28 @@ def test_headline_plane_vs_oracle(name, flag, order, d):
     assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, f"256x256x{d} airfoil, 2 iterations [{name}]")
 
 
+def test_sweep_trace_writes_per_cta_timelines(monkeypatch, tmp_path):
+    """FLUID_SW_TRACE / FLUID_SW_TRACE_AT: the diagnostic that profiles/r02_slab_trace.txt was made with -- per CTA
+    { start, first segment done, end } of the chosen sweep launches; the results are not touched."""
+    from fluid_simulation_b200 import Simulation, masks
+    monkeypatch.setenv("FLUID_SW_TRACE", str(tmp_path / "trace"))
+    monkeypatch.setenv("FLUID_SW_TRACE_AT", "3,9")
+    w, h, d, acc = 128, 40, 24, 6
+    gpu = Simulation(w, h, d, 1, acc=acc, flags=0)
+    cpu = OracleSim(w, h, d, acc=acc, order=ORDER_RB)
+    obs = masks.sphere(w, h, d)
+    gpu.set("obs", obs); cpu.set("obs", obs)
+    gpu.run_iterations(1); cpu.run_iterations(1)
+    assert_bitwise(gpu.state(), cpu.state(), FIELD_NAMES, "traced run")
+    for launch in (3, 9):
+        lines = (tmp_path / f"trace.r0.l{launch}.txt").read_text().splitlines()
+        assert lines[0].startswith("# rank 0 launch")
+        rows = [[int(v) for v in ln.split()] for ln in lines[1:]]
+        assert rows and all(len(r) == 6 for r in rows)
+        busy = [r for r in rows if r[3] < 10 ** 9]
+        assert busy and all(r[1] <= r[3] for r in busy)              # start <= end, in ns from the first start
+
+
 def test_headline_grid_vs_oracle_full_depth():
     """configs[2] at its FULL size (256^3, airfoil, red-black): one run() iteration at acc = 4 (the oracle's
     single thread needs ~40 s for it).  This is the regime the benchmark runs in and no smaller case reaches:
