@@ -1133,7 +1133,6 @@ inline int fl_tiled_solve(fluid_handle* h, int nb, const int* b, const int* fid,
         else if (s->cfg == 1 && g.W <= 256) e = sw_run<2, 4, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         else if (s->cfg == 2 && g.W <= 256) e = sw_run<2, 5, 2>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         else if (s->cfg == 3 && g.W <= 256) e = sw_run<2, 6, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
-        else if (s->cfg == 4 && g.W <= 256) e = sw_run<2, 9, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);   // 16 owned rows: 16 tiles at H = 256 instead of 19
         else if (g.W > 256 && g.W <= 512 && s->cfg != 5) e = sw_run<4, 4, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         else                  e = sw_run<2, 8, 1>(h, per, bb, ff, pp, a, c, jac, xfr, rest, done);
         if (e) return e;
