@@ -181,6 +181,28 @@ class Simulation:
         buf = (C.c_char * max(n, 1)).from_address(ptr)
         return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
+    def stage_field(self, arr):
+        """Pinned host copy of the planes of a padded field that this rank holds (its own planes and its halo
+        planes): make it once, outside any timed region, and hand it to `set_staged` -- the H2D copy then runs
+        from pinned memory (70 MB at 256^3: 1.3 ms instead of ~6 ms from pageable memory)."""
+        from .slab import HALO
+        a = np.asarray(arr, dtype=np.float32).reshape(self.shape)
+        lo = 0 if self.rank == 0 else 1 - HALO
+        hi = self.d_local + 1 if self.rank == self.nranks - 1 else self.d_local + HALO
+        first = self.z_lo + lo - 1
+        buf = self.pinned_array((hi - lo + 1,) + tuple(self.shape[1:]), np.float32)
+        buf[...] = a[first:first + hi - lo + 1]
+        return buf, first
+
+    def set_staged(self, f, staged):
+        """`set(f, arr)` from a `stage_field(arr)` buffer."""
+        buf, first = staged
+        ptr = buf.ctypes.data - first * self.shape[1] * self.shape[2] * 4     # the C ABI takes the base of a whole field
+        if _fid(f) == FIELDS["obs"]:
+            self._ck(self._L.fluid_upload_obstacles(self._h, ptr))
+        else:
+            self._ck(self._L.fluid_upload_field(self._h, _fid(f), ptr))
+
     def add_density_cells(self, xyz, amount):
         """addDensity for n cells at once; xyz int32 (n,3), amount float32 (n,) (host arrays)."""
         self._ck(self._L.fluid_add_density(self._h, len(xyz), xyz.ctypes.data, amount.ctypes.data))

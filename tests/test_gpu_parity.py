@@ -74,6 +74,18 @@ def test_advect_velocity_fused(w, h, d, obstacle):
     check(gpu, cpu, "fused velocity advection")
 
 
+def test_staged_upload_equals_set():
+    """stage_field + set_staged (H2D from a pinned copy of the held planes) leaves the same device state as set()."""
+    from fluid_simulation_b200 import masks
+    gpu, cpu = make_pair(40, 24, 12, 3, 0, ORDER_RB)
+    obs = masks.sphere(40, 24, 12)
+    v = cpu.get("v_y") * 2.0
+    gpu.set_staged("obs", gpu.stage_field(obs)); cpu.set("obs", obs)
+    gpu.set_staged("v_y", gpu.stage_field(v)); cpu.set("v_y", v)
+    gpu.run_iterations(1); cpu.run_iterations(1)
+    check(gpu, cpu, "state after staged uploads")
+
+
 @pytest.mark.parametrize("w,h,d", SIZES)
 def test_divergence_and_gradient(w, h, d):
     gpu, cpu = make_pair(w, h, d, 4, 0, ORDER_RB)
