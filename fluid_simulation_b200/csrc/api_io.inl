@@ -217,13 +217,13 @@ int fluid_dump_frame_async(fluid_handle* h, float* const dst[5])
         if (dst[i] && !h->frame_staging[i]) FL_CUDA(h, cudaMalloc(&h->frame_staging[i], nfl * sizeof(float)));
     // the previous dump must have left the staging buffers before they are overwritten
     if (h->frame_in_flight) FL_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_frame_done, 0));
-    PackBatch pb; int nf = 0;
+    PackBatch pb = {}; int nf = 0;
     for (int i = 0; i < 5; ++i) {
         if (!dst[i]) continue;
         pb.src[nf] = h->field[ids[i]]; pb.dst[nf] = h->frame_staging[i]; ++nf;
     }
     if (nf > 0) {                                         // one snapshot launch for the whole frame
-        const dim3 blk(64, 4), grd((unsigned)((h->g.rows * np + 3) / 4), (unsigned)nf);
+        const dim3 blk(32, 8), grd((unsigned)((h->g.rows * np + 7) / 8), (unsigned)nf);
         k_pack_rows<<<grd, blk, 0, h->stream>>>(h->g, zf, np, pb);
         FL_CHECK_LAUNCH(h);
     }
