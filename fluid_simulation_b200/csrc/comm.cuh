@@ -163,6 +163,25 @@ static inline float* fl_peer_ptr(fluid_handle* h, int r, const float* local)
 
 bool fl_peer_mapped(fluid_handle* h, int r, const float* local) { return fl_peer_ptr(h, r, local) != nullptr; }
 
+// collective, blocking: true on every rank iff `mine` is true on every rank (one-float ncclAllReduce; used once per
+// handle for decisions that must not differ between ranks)
+int fl_all_agree(fluid_handle* h, bool mine, bool* all)
+{
+    SlabComm* c = (SlabComm*)h->comm;
+    if (!c || !c->comm) return fl_fail(h, FLUID_E_COMM, "agreement: no communicator attached");
+    const float v = mine ? 1.0f : 0.0f;
+    float sum = 0.0f;
+    FL_CUDA(h, cudaMemcpyAsync(c->d_token, &v, sizeof v, cudaMemcpyHostToDevice, h->stream));
+    FL_NCCL(h, c, c->AllReduce(c->d_token, c->d_token, 1, ncclFloat, ncclSum, c->comm, h->stream));
+    FL_CUDA(h, cudaMemcpyAsync(&sum, c->d_token, sizeof sum, cudaMemcpyDeviceToHost, h->stream));
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    const float zero = 0.0f;                                              // the barrier's token starts from zero again
+    FL_CUDA(h, cudaMemcpyAsync(c->d_token, &zero, sizeof zero, cudaMemcpyHostToDevice, h->stream));
+    FL_CUDA(h, cudaStreamSynchronize(h->stream));
+    *all = sum == (float)h->nranks;
+    return 0;
+}
+
 // every buffer a sweep can write and the flag block are mapped from both z-neighbours, and the
 // driver offers stream waits on memory: sweeps hand their halos over by peer stores
 static inline bool fl_push_ready(fluid_handle* h);

@@ -44,6 +44,7 @@ struct fluid_handle {
     // set by fl_step_only when it swapped v <-> v_prev instead of copying: the next tiled solve takes its initial
     // guess from the right-hand-side buffer (which holds the very same values) and clears the flag
     unsigned x_from_rhs = 0;         // bit i: batched field i
+    int slab_swap_ok = -1;           // z-slabs: v <-> v_prev swap agreed by all ranks (-1: not asked yet)
     int sm_count = 148;
     size_t l2_persist_max = 0, l2_window_max = 0;   // persisting-L2 carve-out and access-window limits
 };

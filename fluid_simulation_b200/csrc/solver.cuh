@@ -28,6 +28,7 @@ int fl_halo_push(fluid_handle* h, int n, float* const* fields, cudaStream_t stre
 int fl_halo_wait(fluid_handle* h, cudaStream_t stream, unsigned seq);
 int fl_push_targets(fluid_handle* h, int n, float* const* fields, float* (*peer)[4], unsigned** flag, int* zdst);
 bool fl_peer_mapped(fluid_handle* h, int r, const float* local);            // comm.cuh: rank r's copy of this buffer is IPC-mapped
+int fl_all_agree(fluid_handle* h, bool mine, bool* all);                   // comm.cuh: collective AND over the ranks
 int fl_barrier(fluid_handle* h);                                         // comm.cuh
 
 static inline int fl_rebuild_flags(fluid_handle* h)

@@ -1079,16 +1079,24 @@ inline bool fl_swap_instead_of_copy(fluid_handle* h)
     if (off || h->acc <= 0 || !fl_tiled_eligible(h)) return false;
     // z-slabs: every rank swaps the same way, and the peers' mappings are looked up by allocation, so the
     // hand-over follows the buffers; only on the path where the sweeps push their halos themselves
+    StreamState* s = sw_state(h);
+    bool mine = s->encode != nullptr && !s->unbatch;
     if (h->nranks > 1) {
-        if (slab_off || !fl_push_usable(h)) return false;
+        if (h->slab_swap_ok >= 0) return h->slab_swap_ok != 0;
+        if (slab_off || !fl_push_usable(h)) mine = false;
         // advect() gathers from every rank's *_prev buffers, which after a swap are the allocations that held v:
         // both sets must be mapped from everybody (hosts that map only the original gather sources keep the copies)
-        for (int r = 0; r < h->nranks; ++r)
+        for (int r = 0; r < h->nranks && mine; ++r)
             for (int k = 0; k < 3 && r != h->rank; ++k)
-                if (!fl_peer_mapped(h, r, h->field[FLUID_VX + k]) || !fl_peer_mapped(h, r, h->field[FLUID_VX_PREV + k])) return false;
+                if (!fl_peer_mapped(h, r, h->field[FLUID_VX + k]) || !fl_peer_mapped(h, r, h->field[FLUID_VX_PREV + k])) mine = false;
+        // the ranks must not differ in this (a rank that copies while its neighbour swaps reads the wrong buffers):
+        // asked once per handle, at its first step -- a collective like the step itself
+        bool all = false;
+        if (fl_all_agree(h, mine, &all) != 0) all = false;
+        h->slab_swap_ok = all ? 1 : 0;
+        return all;
     }
-    StreamState* s = sw_state(h);
-    return s->encode != nullptr && !s->unbatch;
+    return mine;
 }
 
 // a z-slab runs the density diffusion (simulation.cpp:135) as the fourth field of the velocity diffusion when the
