@@ -9,9 +9,7 @@
 #define SW_SMEM_MAX 232448               // 227 KB of dynamic shared memory per CTA on sm_100
 #define SW_SM_SMEM  233472               // 228 KB of shared memory per SM (each resident CTA also reserves 1 KB)
 
-// column (batched field * row tiles + row tile), planes za..zb; mode bit 0 = streamed downwards,
-// bits 1-2 = 1 + slab face (0 lower, 1 upper) whose two boundary planes this segment hands to the z-neighbour
-struct SwSeg { int col, za, zb, mode; };
+#include "sweep_plan.h"                  // SwSeg and the work decomposition (pure host code)
 
 // 128-bit shared load.  Where only two lanes of the quad are consumed the caller folds the other two
 // into a sink word (sw_lds4_half), otherwise the load is narrowed to two scalar LDS.
