@@ -588,6 +588,7 @@ struct StreamState {
     int face_mode = 2;                                          // FLUID_SW_FACE_CTA: 2 = edge segments first in the CTAs that would otherwise start behind them (plan part 6, one wave), 1 = separate edge CTAs (part 4), 0 = hand-over inside ordinary segments (part 5)
     int edge = SW_EDGE_DEFAULT;                                 // planes per edge segment at an interior slab face (>= 2)
     unsigned long long* trace = nullptr; const char* trace_path = nullptr; long trace_launch = 0, trace_at[2] = { -1, -1 };   // FLUID_SW_TRACE=path, FLUID_SW_TRACE_AT=i,j
+    int segcost = SW_SEGCOST, last_w32 = 32;                    // FLUID_SW_SEGCOST, FLUID_SW_LASTW: the plan's charge per segment start (steps) and the cost of a plane of a ragged last row tile (1/32 of a plane elsewhere)
     int late_extra = -1;                                        // FLUID_SW_LATE: extra pipeline steps the plan charges a CTA that starts behind an edge CTA
     int plan_mode = 2, plan_min_fill = 85;
     // zero-bit volume (k_build_zbits): rebuilt whenever the flag volume was
@@ -613,6 +614,8 @@ inline StreamState* sw_state(fluid_handle* h)
         if (const char* e = getenv("FLUID_SW_EDGE")) { s->edge = atoi(e); if (s->edge < 2) s->edge = 2; }
         if (const char* e = getenv("FLUID_SW_FACE_CTA")) s->face_mode = atoi(e);
         if (const char* e = getenv("FLUID_SW_LATE")) s->late_extra = atoi(e);
+        if (const char* e = getenv("FLUID_SW_SEGCOST")) { s->segcost = atoi(e); if (s->segcost < 1 || s->segcost > 15) s->segcost = SW_SEGCOST; }
+        if (const char* e = getenv("FLUID_SW_LASTW")) { s->last_w32 = atoi(e); if (s->last_w32 < 8 || s->last_w32 > 32) s->last_w32 = 32; }
         if (const char* e = getenv("FLUID_SW_TRACE")) {
             s->trace_path = e;
             if (cudaMalloc(&s->trace, 4096 * 4 * sizeof(unsigned long long)) != cudaSuccess) s->trace = nullptr;
@@ -726,6 +729,7 @@ inline int sw_get_plan(fluid_handle* h, int nb, int ty, int cps, int part, SwPla
         p.sm_count = h->sm_count; p.lo_face = h->rank > 0; p.hi_face = h->rank < h->nranks - 1;
         p.edge = s->edge; p.late_extra = s->late_extra; p.zc_override = s->zc_override;
         p.plan_mode = s->plan_mode; p.plan_min_fill = s->plan_min_fill;
+        p.last_w32 = s->last_w32;
         std::vector<SwSeg> segs; std::vector<int> first;
         sw_build_plan(p, segs, first);
         SwPlan pl;
@@ -777,7 +781,7 @@ inline int sw_run(fluid_handle* h, int nb, const int* b, const int* fid, const i
     const int nbx = nb * nxt;
     SwPlan plan, plan_edge;
     const int plan_part = fused ? (s->face_mode == 2 ? 6 : s->face_mode == 1 ? 4 : 5) : overlap ? 2 : 0;
-    if (int e = sw_get_plan(h, nbx, GE::TY, CPS, plan_part, &plan)) return e;
+    if (int e = sw_get_plan(h, nbx, GE::TY, CPS, plan_part, &plan, s->segcost)) return e;
     if (overlap && !fused) if (int e = sw_get_plan(h, nbx, GE::TY, CPS, 1, &plan_edge)) return e;
     StreamArgs A;
     A.g = g; A.a = a; A.c_recip = 1.0f / c;                              // simulation.cpp:257

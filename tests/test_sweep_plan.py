@@ -22,8 +22,8 @@ def lib(tmp_path_factory):
     return L
 
 
-def build(lib, Dl, H, nb, ty, part, lo=False, hi=False, cps=1, sm=148, edge=8, late=-1, zc=0, mode=2, fill=85):
-    prm = (C.c_int * 14)(Dl, H, nb, ty, cps, part, sm, int(lo), int(hi), edge, late, zc, mode, fill)
+def build(lib, Dl, H, nb, ty, part, lo=False, hi=False, cps=1, sm=148, edge=8, late=-1, zc=0, mode=2, fill=85, lastw=32, segcost=4):
+    prm = (C.c_int * 16)(Dl, H, nb, ty, cps, part, sm, int(lo), int(hi), edge, late, zc, mode, fill, lastw, segcost)
     cap = 1 << 16
     segs = np.zeros((cap, 4), np.int32); first = np.zeros(cap, np.int32)
     ns, nc = C.c_int(0), C.c_int(0)
@@ -91,6 +91,10 @@ def test_knobs_keep_the_cover(lib, late, edge):
     for mode in (0, 1, 2):
         built, segs, first = build(lib, 256, 256, 1, 14, 0, mode=mode)
         check(built, segs, first, 256, 256, 1, 14, False, False, edge)
+    for lastw, segcost in ((30, 5), (24, 4), (32, 7), (8, 1), (29, 15)):       # FLUID_SW_LASTW / FLUID_SW_SEGCOST
+        for (Dl, H, nb, part, lo, hi) in ((256, 256, 4, 0, False, False), (256, 256, 1, 6, True, True), (100, 250, 3, 4, True, False)):
+            built, segs, first = build(lib, Dl, H, nb, 14, part, lo, hi, edge=edge, late=late, lastw=lastw, segcost=segcost)
+            check(built, segs, first, Dl, H, nb, 14, lo, hi, edge)
 
 
 def test_benchmark_shapes_have_the_grids_the_traces_show(lib):
